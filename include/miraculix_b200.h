@@ -1,0 +1,141 @@
+/* miraculix_b200.h -- C ABI of the B200-native compressed-genotype library.
+ *
+ * PART 1 re-exports, symbol for symbol, what the reference's bindings bind for this path
+ * (citations relative to the reference tree):
+ *   - Fortran bind(C) interfaces   src/bindings/Fortran/mod5codesapi.f90:22-82
+ *   - Julia ccall sites            src/bindings/Julia/dgemm_compressed.jl:55-57,88,129-131,154
+ *                                  src/bindings/Julia/crossproduct.jl:54-58
+ *   - C declarations               src/miraculix/5codes.h:137-153, src/cuda/snp_multiply_cuda.h:113-114
+ * so that `libmiraculix_b200.so` can be dlopen'ed in place of `src/miraculix/miraculix.so`
+ * (see INTEGRATION.md).  PART 2 is additive (prefix mb200_): device-pointer variants so an
+ * iterative solver can stay on the GPU, the fused GRM / LD epilogues, introspection used by the
+ * parity tests, and an on-device simulator for benchmark-sized inputs.
+ *
+ * All arrays in PART 1 are caller-owned HOST memory borrowed for the duration of the call.
+ * There is no CPU fallback anywhere: every entry point runs hand-written sm_100a kernels and
+ * reports an error (stderr + status) if no CUDA device is usable.
+ */
+#ifndef MIRACULIX_B200_H
+#define MIRACULIX_B200_H
+
+#include <stdbool.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * PART 1 -- reference-compatible surface
+ * ---------------------------------------------------------------------------------------- */
+
+/* replaces src/miraculix/5codesAPI.c:43-70 (-> setOptions5, 5codesChar.cc:165-209).
+ * Process-global.  The GPU-compatible combination is enforced exactly like the reference
+ * (5codesChar.cc:192-193): use_miraculix_freq must be 0, ignore_missings must be 1,
+ * do_normalize must be 0, otherwise: message on stderr and exit(EXIT_FAILURE).
+ * use_gpu == 0 is accepted but the work still runs on the GPU (this build has no CPU path). */
+void setOptions_compressed(int use_gpu, int cores, int floatLoop, int meanSubstract,
+                           int ignore_missings, int do_not_center, int do_normalize,
+                           int use_miraculix_freq, int variant, int print_details);
+
+/* replaces src/miraculix/5codesAPI.c:80-96 (-> plinkToSxI 5codesChar.cc:344-399 -> plink2gpu
+ * src/cuda/dgemm_compressed_cuda.cu:43-170).
+ * plink: SNP-major .bed payload, snps rows of ceil(indiv/4) bytes.  plink_transposed is
+ * accepted for signature compatibility and NOT read (may be NULL or alias plink): both device
+ * orientations are produced by the GPU repack.  f: allele frequencies, length snps (copied).
+ * On failure *compressed is set to NULL (Julia checks this, dgemm_compressed.jl:90). */
+void plink2compressed(char *plink, char *plink_transposed, int snps, int indiv, double *f,
+                      int max_n, void **compressed);
+
+/* replaces src/miraculix/5codesAPI.c:98-110 (-> dgemm_compressed_gpu,
+ * src/cuda/dgemm_compressed_cuda.cu:218-489).
+ *   'N'/'n':          C[indiv x n] = (Z - 2 1 f^T)   B[snps  x n]
+ *   'T'/'t'/'Y'/'y':  C[snps  x n] = (Z - 2 1 f^T)^T B[indiv x n]
+ * any other first byte: exit(99) as 5codesAPI.c:73-77.  B, C column-major; Ldb/Ldc are
+ * honoured (the reference GPU path silently assumes Ldb = rows(B), Ldc = rows(C)).
+ * n > max_n is an error (message, C untouched) instead of the reference's scratch overflow. */
+void dgemm_compressed(char *trans, void *compressed, int n, double *B, int Ldb, double *C, int Ldc);
+
+/* replaces src/miraculix/5codesAPI.c:159-161 (-> freegpu dgemm_compressed_cuda.cu:176-213).
+ * Unlike the reference this also sets *compressed = NULL. */
+void free_compressed(void **compressed);
+
+/* replaces src/miraculix/5codesAPI.c:37-39; works for GPU handles (host copy of f kept). */
+void get_compressed_freq(void *compressed, double *f);
+
+/* replaces src/cuda/snp_multiply_cuda.cu:375-382 (-> snp_crossproduct :38-368).
+ * snp_matrix: `indiv` rows of ceil(snps/4) bytes, 2-bit fields; the field is the value unless
+ * is_plink_format, in which case every byte first goes through the reference's PLINK->2bit
+ * table (src/cuda/snp_multiply_cuda.h:202).  ans: indiv x indiv doubles, column-major, full
+ * symmetric matrix of exact integer counts.  Returns 0 on success, 1 on error. */
+int snp_multiply_gpu(unsigned char *snp_matrix, int snps, int indiv, double *ans,
+                     bool is_plink_format);
+
+/* ------------------------------------------------------------------------------------------
+ * PART 2 -- additive entry points (not in the reference)
+ * ---------------------------------------------------------------------------------------- */
+
+/* Status of the last call on this thread: 0 ok, else cudaError / internal code; message text. */
+int mb200_last_status(void);
+const char *mb200_last_message(void);
+/* Number of kernels this library has launched since load (bench.py "gpu_launches"). */
+unsigned long long mb200_kernel_launches(void);
+/* 0: fp64 SIMT streaming kernel.  1: exact int8-slice tcgen05 kernel (default when built).
+ * slices: number of 8-bit digits each column of B is split into (5..8, default 7). */
+int mb200_set_dgemm_mode(int mode, int slices);
+/* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct (default). */
+int mb200_set_crossprod_mode(int mode);
+
+/* dgemm_compressed with DEVICE pointers dB, dC on the handle's device; asynchronous on the
+ * handle's stream (mb200_stream).  trans: 0 = 'N', 1 = 'T'.  Returns 0 / error code. */
+int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
+                                  double *dC, long ldc);
+void *mb200_stream(void *compressed); /* cudaStream_t */
+int mb200_sync(void *compressed);
+
+/* Build a handle from a bed payload that already lives on the device (same layout as the
+ * host one).  d_f may be NULL: then f is computed on the device from the allele counts. */
+int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long indiv,
+                                  const double *d_f, int max_n, void **compressed);
+
+/* Introspection for the parity tests: device layout of a handle (DESIGN.md "HBM layout"). */
+typedef struct {
+  long snps, indiv;
+  long pitch_snp_major;    /* bytes per SNP row        (multiple of 128) */
+  long pitch_indiv_major;  /* bytes per individual row (multiple of 128) */
+  const unsigned char *d_snp_major;
+  const unsigned char *d_indiv_major;
+  const double *d_f;
+  const unsigned long long *d_allele_counts; /* sum_i z_is per SNP, computed by the repack */
+  int device;
+} mb200_layout;
+int mb200_get_layout(void *compressed, mb200_layout *out);
+/* Download both repacked orientations (padded rows) and the allele counts to host buffers. */
+int mb200_download_layout(void *compressed, unsigned char *snp_major, unsigned char *indiv_major,
+                          unsigned long long *allele_counts);
+
+/* On-device simulator of PLINK genotypes (benchmark-sized inputs never cross PCIe):
+ * p_j ~ U(0.1,0.6), z_ij ~ Binomial(2,p_j), counter-based RNG keyed by (seed, snp, indiv).
+ * d_plink: snps x ceil(indiv/4) bytes on the current device. */
+int mb200_simulate_plink_device(unsigned char *d_plink, long snps, long indiv,
+                                unsigned long long seed);
+
+/* Crossproduct on device-resident input.  d_x: rows x ceil(k/4) bytes.  d_counts (optional,
+ * may be NULL): rows x rows int32 row-major upper-triangle-valid scratch is internal; d_ans:
+ * rows x rows doubles column-major.  mode: 0 raw counts, 1 centred GRM (crossproduct.jl:91-106;
+ * d_f = allele freq length k, do_scale), 2 LD (crossproduct.jl:128-152; n_obs = k). */
+int mb200_crossprod_device(const unsigned char *d_x, long k, long rows, int is_plink_format,
+                           int mode, const double *d_f, int do_scale, double *d_ans);
+/* Host-pointer convenience wrappers of the above (same arguments as snp_multiply_gpu + f). */
+int mb200_grm(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool is_plink_format,
+              const double *f, bool do_scale);
+int mb200_ld(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool is_plink_format,
+             const double *f);
+/* Timing of the device part of the last crossproduct call on this thread, in milliseconds:
+ * [0] expand+GEMM, [1] epilogue (int32 -> fp64, symmetrise, centre), [2] executed int8 ops. */
+int mb200_crossprod_last_timing(double out[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIRACULIX_B200_H */

@@ -1,0 +1,222 @@
+"""Host-side mirror of the reference's Julia bindings over the C-ABI of libmiraculix_b200.so.
+
+Function names and argument meaning follow
+  src/bindings/Julia/dgemm_compressed.jl:42-155  (set_options, init_compressed, dgemm_compressed, free_compressed)
+  src/bindings/Julia/crossproduct.jl:44-152      (snp_crossprod, grm, ld)
+of the reference so that tests read like tests/dgemm_compressed/test.jl and
+tests/crossproduct/test_grm.jl.  Everything here is ctypes plumbing: no arithmetic happens in
+Python, and there is no CPU fallback -- a missing library or GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmiraculix_b200.so")
+_LIB = None
+
+
+class Layout(C.Structure):
+    _fields_ = [("snps", C.c_long), ("indiv", C.c_long), ("pitch_snp_major", C.c_long),
+                ("pitch_indiv_major", C.c_long), ("d_snp_major", C.c_void_p),
+                ("d_indiv_major", C.c_void_p), ("d_f", C.c_void_p), ("d_allele_counts", C.c_void_p),
+                ("device", C.c_int)]
+
+
+# every symbol include/miraculix_b200.h declares: (restype, argtypes)
+SIGNATURES = {
+    "setOptions_compressed": (None, [C.c_int] * 10),
+    "plink2compressed": (None, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                C.POINTER(C.c_void_p)]),
+    "dgemm_compressed": (None, [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                C.c_int]),
+    "free_compressed": (None, [C.POINTER(C.c_void_p)]),
+    "get_compressed_freq": (None, [C.c_void_p, C.c_void_p]),
+    "snp_multiply_gpu": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool]),
+    "mb200_last_status": (C.c_int, []),
+    "mb200_last_message": (C.c_char_p, []),
+    "mb200_kernel_launches": (C.c_ulonglong, []),
+    "mb200_set_dgemm_mode": (C.c_int, [C.c_int, C.c_int]),
+    "mb200_set_crossprod_mode": (C.c_int, [C.c_int]),
+    "mb200_dgemm_compressed_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
+                                                C.c_void_p, C.c_long]),
+    "mb200_stream": (C.c_void_p, [C.c_void_p]),
+    "mb200_sync": (C.c_int, [C.c_void_p]),
+    "mb200_plink2compressed_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_void_p, C.c_int,
+                                                C.POINTER(C.c_void_p)]),
+    "mb200_get_layout": (C.c_int, [C.c_void_p, C.POINTER(Layout)]),
+    "mb200_download_layout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mb200_simulate_plink_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_ulonglong]),
+    "mb200_crossprod_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_int,
+                                         C.c_void_p, C.c_int, C.c_void_p]),
+    "mb200_grm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool, C.c_void_p, C.c_bool]),
+    "mb200_ld": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool, C.c_void_p]),
+    "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
+}
+
+
+def load_library(path: str | None = None):
+    """dlopen the C-ABI library (cf. load_shared_library, src/bindings/Julia/miraculix.jl)."""
+    global _LIB
+    if _LIB is not None and path is None:
+        return _LIB
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} not built: run `python -m miraculix_b200.build` "
+                           "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype, fn.argtypes = res, args
+    _LIB = lib
+    return lib
+
+
+class MiraculixError(RuntimeError):
+    pass
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load_library().mb200_last_message().decode(errors="replace")
+        raise MiraculixError(f"{what} failed ({rc}): {msg}")
+
+
+def last_status() -> int:
+    return load_library().mb200_last_status()
+
+
+def kernel_launches() -> int:
+    return int(load_library().mb200_kernel_launches())
+
+
+def set_options(use_gpu: bool = True, cores: int = 0, not_center: bool = False, variant: int = 0,
+                verbose: int = 0) -> None:
+    """dgemm_compressed.jl:42-58 -- same flag vector: floatLoop=0, meanSubstract=0,
+    ignore_missings=1, do_normalize=0, use_miraculix_freq=0."""
+    load_library().setOptions_compressed(int(use_gpu), cores, 0, 0, 1, int(not_center), 0, 0,
+                                         variant, verbose)
+
+
+def init_compressed(plink: np.ndarray, snps: int, indiv: int, freq: np.ndarray, max_ncol: int,
+                    plink_transposed: np.ndarray | None = None) -> C.c_void_p:
+    """dgemm_compressed.jl:81-92.  ``plink``: (snps, ceil(indiv/4)) uint8 rows = SNPs (the Julia
+    matrix is (ceil(indiv/4), snps) column-major: same memory).  ``plink_transposed`` is accepted
+    and ignored -- the GPU repack produces both orientations."""
+    plink = np.ascontiguousarray(plink, dtype=np.uint8)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    if plink.shape != (snps, (indiv + 3) // 4):
+        raise ValueError(f"plink has shape {plink.shape}, expected {(snps, (indiv + 3) // 4)}")
+    if freq.shape != (snps,):
+        raise ValueError("freq must have length snps")
+    handle = C.c_void_p(None)
+    tp = plink_transposed.ctypes.data if plink_transposed is not None else plink.ctypes.data
+    load_library().plink2compressed(plink.ctypes.data, tp, snps, indiv, freq.ctypes.data, max_ncol,
+                                    C.byref(handle))
+    if not handle.value:  # dgemm_compressed.jl:90
+        raise MiraculixError("plink2compressed returned NULL: " +
+                             load_library().mb200_last_message().decode(errors="replace"))
+    return handle
+
+
+def dgemm_compressed(trans: str, handle: C.c_void_p, B: np.ndarray, snps: int, indiv: int,
+                     out: np.ndarray | None = None) -> np.ndarray:
+    """dgemm_compressed.jl:115-134: 'N' -> (indiv x n) = (Z - 2 1 f^T) B, 'T' -> (snps x n)."""
+    t = trans in "TtYy"
+    B = np.asfortranarray(B, dtype=np.float64)
+    if B.ndim == 1:
+        B = B.reshape(-1, 1, order="F")
+    k, n = B.shape
+    m = snps if t else indiv
+    if k != (indiv if t else snps):
+        raise ValueError(f"B has {k} rows, expected {indiv if t else snps}")
+    if out is None:
+        out = np.zeros((m, n), dtype=np.float64, order="F")
+    lib = load_library()
+    lib.dgemm_compressed(trans.encode()[:1], handle, n, B.ctypes.data, k, out.ctypes.data, m)
+    _check(lib.mb200_last_status(), "dgemm_compressed")
+    return out
+
+
+def free_compressed(handle: C.c_void_p) -> None:
+    """dgemm_compressed.jl:150-155."""
+    load_library().free_compressed(C.byref(handle))
+
+
+def get_compressed_freq(handle: C.c_void_p, snps: int) -> np.ndarray:
+    f = np.zeros(snps, dtype=np.float64)
+    load_library().get_compressed_freq(handle, f.ctypes.data)
+    return f
+
+
+def get_layout(handle: C.c_void_p) -> Layout:
+    lay = Layout()
+    _check(load_library().mb200_get_layout(handle, C.byref(lay)), "mb200_get_layout")
+    return lay
+
+
+def download_layout(handle: C.c_void_p):
+    """(snp_major[snps, pitch_s], indiv_major[indiv, pitch_i], allele_counts[snps]) from HBM."""
+    lay = get_layout(handle)
+    sm = np.zeros((lay.snps, lay.pitch_snp_major), dtype=np.uint8)
+    im = np.zeros((lay.indiv, lay.pitch_indiv_major), dtype=np.uint8)
+    cnt = np.zeros(lay.snps, dtype=np.uint64)
+    _check(load_library().mb200_download_layout(handle, sm.ctypes.data, im.ctypes.data,
+                                                cnt.ctypes.data), "mb200_download_layout")
+    return sm, im, cnt
+
+
+def _check_packed(x: np.ndarray, k: int, rows: int) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.uint8)
+    if x.shape != (rows, (k + 3) // 4):  # check_dimensions, crossproduct.jl:51
+        raise ValueError(f"matrix has shape {x.shape}, expected {(rows, (k + 3) // 4)}")
+    return x
+
+
+def snp_crossprod(x: np.ndarray, snps: int, indiv: int, is_snpmajor: bool,
+                  is_plink_format: bool = False) -> np.ndarray:
+    """crossproduct.jl:44-64.  is_snpmajor=False: x = (indiv, ceil(snps/4)) -> Z Z^T (indiv^2);
+    is_snpmajor=True: x = (snps, ceil(indiv/4)) -> Z^T Z (snps^2)."""
+    nrow, ncol = (indiv, snps) if is_snpmajor else (snps, indiv)
+    x = _check_packed(x, nrow, ncol)
+    M = np.zeros((ncol, ncol), dtype=np.float64, order="F")
+    rc = load_library().snp_multiply_gpu(x.ctypes.data, nrow, ncol, M.ctypes.data, is_plink_format)
+    _check(rc, "snp_multiply_gpu")
+    return M
+
+
+def grm(x: np.ndarray, snps: int, indiv: int, is_plink_format: bool = False, do_scale: bool = True,
+        allele_freq: np.ndarray | None = None) -> np.ndarray:
+    """crossproduct.jl:83-110, with the centring/scaling epilogue fused on the GPU."""
+    if do_scale and (allele_freq is None or len(allele_freq) != snps):
+        raise ValueError(f"Allele frequencies need to be equal to length of SNPs {snps}.")
+    x = _check_packed(x, snps, indiv)
+    f = np.ascontiguousarray(allele_freq, dtype=np.float64) if allele_freq is not None else None
+    M = np.zeros((indiv, indiv), dtype=np.float64, order="F")
+    rc = load_library().mb200_grm(x.ctypes.data, snps, indiv, M.ctypes.data, is_plink_format,
+                                  f.ctypes.data if f is not None else None, do_scale)
+    _check(rc, "mb200_grm")
+    return M
+
+
+def ld(x: np.ndarray, snps: int, indiv: int, is_plink_format: bool = False,
+       allele_freq: np.ndarray | None = None) -> np.ndarray:
+    """crossproduct.jl:128-152: x SNP-major (snps, ceil(indiv/4))."""
+    if allele_freq is None or len(allele_freq) != snps:
+        raise ValueError(f"Allele frequencies need to be equal to length of SNPs {snps}.")
+    x = _check_packed(x, indiv, snps)
+    f = np.ascontiguousarray(allele_freq, dtype=np.float64)
+    M = np.zeros((snps, snps), dtype=np.float64, order="F")
+    rc = load_library().mb200_ld(x.ctypes.data, indiv, snps, M.ctypes.data, is_plink_format,
+                                 f.ctypes.data)
+    _check(rc, "mb200_ld")
+    return M
+
+
+def crossprod_last_timing():
+    out = (C.c_double * 3)()
+    load_library().mb200_crossprod_last_timing(C.byref(out))
+    return {"gemm_ms": out[0], "epilogue_ms": out[1], "executed_ops": out[2]}

@@ -1,0 +1,488 @@
+// abi.cu -- the C-ABI of libmiraculix_b200.so (include/miraculix_b200.h).
+// Host-side replacement of the reference's boundary and dispatch layers:
+//   src/miraculix/5codesAPI.c:37-161   (the exported symbols)
+//   src/miraculix/5codesChar.cc:165-209, :344-449  (setOptions5, plinkToSxI, *5api, free5)
+//   src/cuda/cuda_utils.cu:44-248      (PRINT_LEVEL / CUDA_DEVICE handling, error printing)
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+#include "../../include/miraculix_b200.h"
+#include "common.cuh"
+#include "handle.h"
+
+namespace mb200 {
+
+std::atomic<unsigned long long> g_kernel_launches{0};
+
+static thread_local Status t_status;
+static thread_local CrossprodTiming t_cp_timing;
+Status &status() { return t_status; }
+void clear_status() { t_status.code = 0; t_status.msg[0] = 0; }
+
+int fail(int code, const char *func, int line, const char *fmt, ...) {
+  Status &s = status();
+  s.code = code ? code : -1;
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(s.msg, sizeof(s.msg), fmt, ap);
+  va_end(ap);
+  // reference style (cuda_utils.cu:84-118): always print, caller decides what to do
+  fprintf(stderr, "miraculix_b200: error in %s (line %d): %s\n", func, line, s.msg);
+  return s.code;
+}
+
+int print_level() {
+  static int lvl = -100;
+  if (lvl == -100) {
+    const char *e = getenv("PRINT_LEVEL");
+    lvl = e ? atoi(e) : -1;  // quiet by default
+  }
+  return lvl;
+}
+
+Options &options() {
+  static Options o;
+  static bool init = false;
+  if (!init) {
+    init = true;
+    if (const char *e = getenv("MB200_DGEMM_MODE")) o.dgemm_mode = atoi(e);
+    if (const char *e = getenv("MB200_DGEMM_SLICES")) o.dgemm_slices = atoi(e);
+    if (const char *e = getenv("MB200_CROSSPROD_MODE")) o.crossprod_mode = atoi(e);
+  }
+  return o;
+}
+
+int device_sm_count(int device) {
+  static int cache[64] = {0};
+  if (device < 0 || device >= 64) return 148;
+  if (!cache[device]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0)
+      n = 148;
+    cache[device] = n;
+  }
+  return cache[device];
+}
+
+// CUDA_DEVICE env selects the ordinal (reference cuda_utils.cu:188-248); unlike the reference,
+// an unset CUDA_VISIBLE_DEVICES is not an error, and without CUDA_DEVICE the calling thread's
+// current device is kept (so torch.cuda.set_device / cudaSetDevice callers are respected).
+int select_device() {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0) {
+    fail((int)(e ? e : cudaErrorNoDevice), __func__, __LINE__,
+         "no usable CUDA device (%s); this library has no CPU path",
+         cudaGetErrorString(e ? e : cudaErrorNoDevice));
+    return -1;
+  }
+  int dev = -1;
+  if (const char *env = getenv("CUDA_DEVICE")) dev = atoi(env);
+  if (dev < 0) {
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  }
+  if (dev >= count) {
+    fail(-4, __func__, __LINE__, "CUDA_DEVICE=%d but only %d device(s) visible", dev, count);
+    return -1;
+  }
+  if (cudaSetDevice(dev) != cudaSuccess) {
+    fail(-4, __func__, __LINE__, "cudaSetDevice(%d) failed", dev);
+    return -1;
+  }
+  cudaDeviceProp p;
+  if (cudaGetDeviceProperties(&p, dev) == cudaSuccess && p.major != 10)
+    fprintf(stderr, "miraculix_b200: warning: device %d is sm_%d%d; kernels are built for sm_100a\n",
+            dev, p.major, p.minor);
+  return dev;
+}
+
+Handle *as_handle(void *p) {
+  Handle *h = reinterpret_cast<Handle *>(p);
+  if (!h || h->magic != kHandleMagic) {
+    fail(-5, __func__, __LINE__, "invalid compressed handle %p", p);
+    return nullptr;
+  }
+  if (cudaSetDevice(h->device) != cudaSuccess) {
+    fail(-4, __func__, __LINE__, "cudaSetDevice(%d) failed", h->device);
+    return nullptr;
+  }
+  return h;
+}
+
+static void destroy_handle(Handle *h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  cudaFree(h->d_snp_major);
+  cudaFree(h->d_indiv_major);
+  cudaFree(h->d_f);
+  cudaFree(h->d_counts);
+  cudaFree(h->d_B);
+  cudaFree(h->d_C);
+  cudaFree(h->d_w);
+  cudaFree(h->d_Bq);
+  if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  h->magic = 0;
+  delete h;
+}
+
+// Allocate everything a handle owns (device layout + per-call scratch); no repack yet.
+static int create_handle(long snps, long indiv, int max_n, Handle **out) {
+  *out = nullptr;
+  if (snps <= 0 || indiv <= 0) return fail(-2, __func__, __LINE__, "snps=%ld indiv=%ld", snps, indiv);
+  if (max_n < 1) max_n = 1;
+  const int dev = select_device();
+  if (dev < 0) return status().code;
+  Handle *h = new (std::nothrow) Handle();
+  if (!h) return fail(-6, __func__, __LINE__, "out of host memory");
+  h->device = dev;
+  h->snps = snps;
+  h->indiv = indiv;
+  h->max_n = max_n;
+  h->pitch_s = round_up(ceil_div(indiv, 4), 128);
+  h->pitch_i = round_up(ceil_div(snps, 4), 128);
+  h->sm_count = device_sm_count(dev);
+  const long mx = snps > indiv ? snps : indiv;
+#define H_CUDA(expr)                                                                  \
+  do {                                                                                \
+    cudaError_t _e = (expr);                                                          \
+    if (_e != cudaSuccess) {                                                          \
+      int rc = fail((int)_e, __func__, __LINE__, "%s: %s", #expr, cudaGetErrorString(_e)); \
+      destroy_handle(h);                                                              \
+      return rc;                                                                      \
+    }                                                                                 \
+  } while (0)
+  H_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  H_CUDA(cudaEventCreate(&h->ev0));
+  H_CUDA(cudaEventCreate(&h->ev1));
+  H_CUDA(cudaMalloc(&h->d_snp_major, (size_t)snps * h->pitch_s));
+  H_CUDA(cudaMalloc(&h->d_indiv_major, (size_t)indiv * h->pitch_i));
+  H_CUDA(cudaMalloc(&h->d_f, sizeof(double) * snps));
+  H_CUDA(cudaMalloc(&h->d_counts, sizeof(unsigned long long) * snps));
+  H_CUDA(cudaMalloc(&h->d_B, sizeof(double) * mx * max_n));
+  H_CUDA(cudaMalloc(&h->d_C, sizeof(double) * mx * max_n));
+  H_CUDA(cudaMalloc(&h->d_w, sizeof(double) * 4 * (max_n + 16)));
+  H_CUDA(cudaMemsetAsync(h->d_snp_major, 0, (size_t)snps * h->pitch_s, h->stream));
+  H_CUDA(cudaMemsetAsync(h->d_indiv_major, 0, (size_t)indiv * h->pitch_i, h->stream));
+  H_CUDA(cudaMemsetAsync(h->d_counts, 0, sizeof(unsigned long long) * snps, h->stream));
+#undef H_CUDA
+  *out = h;
+  return 0;
+}
+
+int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count);
+
+// Host bed -> device layout: stream the bed through two device staging buffers in chunks of
+// whole 256-SNP tiles and repack each chunk as it lands.
+static int repack_from_host(Handle *h, const uint8_t *plink) {
+  const long bs = ceil_div(h->indiv, 4);
+  long rows_per_chunk = (256L << 20) / bs / 256 * 256;
+  if (rows_per_chunk < 256) rows_per_chunk = 256;
+  if (rows_per_chunk > round_up(h->snps, 256)) rows_per_chunk = round_up(h->snps, 256);
+  uint8_t *stage[2] = {nullptr, nullptr};
+  cudaEvent_t done[2];
+  for (int i = 0; i < 2; i++) {
+    MB_CUDA(cudaMalloc(&stage[i], (size_t)rows_per_chunk * bs));
+    MB_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+  }
+  int rc = 0, b = 0;
+  for (long s = 0; s < h->snps && rc == 0; s += rows_per_chunk, b ^= 1) {
+    const long cnt = h->snps - s < rows_per_chunk ? h->snps - s : rows_per_chunk;
+    cudaEventSynchronize(done[b]);  // staging buffer free again
+    cudaError_t e = cudaMemcpyAsync(stage[b], plink + s * bs, (size_t)cnt * bs,
+                                    cudaMemcpyHostToDevice, h->stream);
+    if (e != cudaSuccess) { rc = fail((int)e, __func__, __LINE__, "H2D bed: %s", cudaGetErrorString(e)); break; }
+    rc = repack_chunk(h, stage[b], s, cnt);
+    cudaEventRecord(done[b], h->stream);
+  }
+  cudaStreamSynchronize(h->stream);
+  for (int i = 0; i < 2; i++) {
+    cudaFree(stage[i]);
+    cudaEventDestroy(done[i]);
+  }
+  return rc;
+}
+
+}  // namespace mb200
+
+using namespace mb200;
+
+extern "C" {
+
+int mb200_last_status(void) { return status().code; }
+const char *mb200_last_message(void) { return status().msg; }
+unsigned long long mb200_kernel_launches(void) { return g_kernel_launches.load(); }
+
+int mb200_set_dgemm_mode(int mode, int slices) {
+  Options &o = options();
+  if (mode == 0 || mode == 1) o.dgemm_mode = mode;
+  if (slices >= 3 && slices <= 8) o.dgemm_slices = slices;
+  return 0;
+}
+int mb200_set_crossprod_mode(int mode) {
+  if (mode == 0 || mode == 1) options().crossprod_mode = mode;
+  return 0;
+}
+
+void setOptions_compressed(int use_gpu, int cores, int floatLoop, int meanSubstract,
+                           int ignore_missings, int do_not_center, int do_normalize,
+                           int use_miraculix_freq, int variant, int print_details) {
+  (void)floatLoop; (void)meanSubstract;
+  Options &o = options();
+  // same admissible combination as the reference GPU path (5codesChar.cc:192-193): external
+  // frequencies, missings decoded as 0, no normalising; violation = message + exit like ERR0.
+  if (use_miraculix_freq || !ignore_missings || do_normalize) {
+    fprintf(stderr,
+            "miraculix_b200: in case of 'gpu' the Fortran frequency must always be used; "
+            "missings/centering/normalizing cannot treated.\n");
+    exit(EXIT_FAILURE);
+  }
+  if (cores == 0) {
+    const char *s = getenv("OMP_NUM_THREADS");
+    if (s) cores = atoi(s);
+    if (cores <= 0) cores = 4;  // 5codesChar.cc:177-187
+  }
+  o.use_gpu = use_gpu;
+  o.cores = cores;
+  o.centered = !do_not_center;
+  o.variant = variant < 32 ? 32 : variant > 256 ? 256 : variant;
+  o.print_details = print_details;
+  if (print_details > 0 || print_level() > 0) {
+    printf("miraculix_b200 options: gpu=always centered=%d cores=%d (host threads unused on the "
+           "GPU path)%s\n", o.centered, o.cores,
+           use_gpu ? "" : "  [use_gpu=0 requested: this build has no CPU path]");
+  }
+}
+
+int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long indiv,
+                                  const double *d_f, int max_n, void **compressed) {
+  clear_status();
+  if (!compressed) return fail(-2, __func__, __LINE__, "compressed == NULL");
+  *compressed = nullptr;
+  Handle *h = nullptr;
+  MB_CHECK(create_handle(snps, indiv, max_n, &h));
+  int rc = repack_from_device(h, d_plink);
+  if (!rc) {
+    if (d_f) {
+      cudaError_t e = cudaMemcpyAsync(h->d_f, d_f, sizeof(double) * snps, cudaMemcpyDeviceToDevice,
+                                      h->stream);
+      if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+    } else {
+      rc = freq_from_counts(h);
+    }
+  }
+  if (!rc) {
+    h->h_f.resize(snps);
+    cudaError_t e = cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * snps,
+                                    cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+  }
+  if (rc) { destroy_handle(h); return rc; }
+  *compressed = h;
+  return 0;
+}
+
+void plink2compressed(char *plink, char *plink_transposed, int snps, int indiv, double *f,
+                      int max_n, void **compressed) {
+  (void)plink_transposed;  // both orientations are produced on the GPU from `plink`
+  clear_status();
+  if (!compressed) { fail(-2, __func__, __LINE__, "compressed == NULL"); return; }
+  *compressed = nullptr;
+  if (!plink || !f) { fail(-2, __func__, __LINE__, "plink or f is NULL"); return; }
+  Handle *h = nullptr;
+  if (create_handle(snps, indiv, max_n, &h)) return;
+  int rc = repack_from_host(h, reinterpret_cast<const uint8_t *>(plink));
+  if (!rc) {
+    h->h_f.assign(f, f + snps);
+    cudaError_t e = cudaMemcpyAsync(h->d_f, f, sizeof(double) * snps, cudaMemcpyHostToDevice,
+                                    h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+  }
+  if (rc) { destroy_handle(h); return; }
+  if (print_level() > 0)
+    printf("miraculix_b200: %d SNPs x %d individuals resident on device %d (%.1f MB)\n", snps,
+           indiv, h->device, ((double)snps * h->pitch_s + (double)indiv * h->pitch_i) / 1e6);
+  *compressed = h;
+}
+
+int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
+                                  double *dC, long ldc) {
+  clear_status();
+  Handle *h = as_handle(compressed);
+  if (!h) return status().code;
+  const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
+  if (n < 0 || ldb < k || ldc < m)
+    return fail(-2, __func__, __LINE__, "bad arguments n=%d ldb=%ld (k=%ld) ldc=%ld (m=%ld)", n, ldb,
+                k, ldc, m);
+  return dgemm_device(h, trans ? 1 : 0, n, dB, ldb, dC, ldc);
+}
+
+void *mb200_stream(void *compressed) {
+  Handle *h = as_handle(compressed);
+  return h ? (void *)h->stream : nullptr;
+}
+int mb200_sync(void *compressed) {
+  Handle *h = as_handle(compressed);
+  if (!h) return status().code;
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+static int is_trans(const char *trans) {  // 5codesAPI.c:73-77
+  if (*trans == 'T' || *trans == 't' || *trans == 'Y' || *trans == 'y') return 1;
+  if (*trans != 'N' && *trans != 'n') exit(99);
+  return 0;
+}
+
+static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, double *C, long ldc) {
+  const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
+  if (n > h->max_n)
+    return fail(-2, __func__, __LINE__, "n=%d exceeds max_n=%d given to plink2compressed", n, h->max_n);
+  if (ldb < k || ldc < m)
+    return fail(-2, __func__, __LINE__, "leading dimension too small: ldb=%ld (need %ld) ldc=%ld (need %ld)",
+                ldb, k, ldc, m);
+  if (n <= 0) return 0;
+  if (ldb == k)
+    MB_CUDA(cudaMemcpyAsync(h->d_B, B, sizeof(double) * k * n, cudaMemcpyHostToDevice, h->stream));
+  else
+    MB_CUDA(cudaMemcpy2DAsync(h->d_B, sizeof(double) * k, B, sizeof(double) * ldb,
+                              sizeof(double) * k, n, cudaMemcpyHostToDevice, h->stream));
+  MB_CHECK(dgemm_device(h, trans, n, h->d_B, k, h->d_C, m));
+  if (ldc == m)
+    MB_CUDA(cudaMemcpyAsync(C, h->d_C, sizeof(double) * m * n, cudaMemcpyDeviceToHost, h->stream));
+  else
+    MB_CUDA(cudaMemcpy2DAsync(C, sizeof(double) * ldc, h->d_C, sizeof(double) * m,
+                              sizeof(double) * m, n, cudaMemcpyDeviceToHost, h->stream));
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+void dgemm_compressed(char *trans, void *compressed, int n, double *B, int Ldb, double *C, int Ldc) {
+  clear_status();
+  const int t = is_trans(trans);
+  Handle *h = as_handle(compressed);
+  if (!h) return;
+  dgemm_host(h, t, n, B, Ldb, C, Ldc);
+}
+
+void free_compressed(void **compressed) {
+  clear_status();
+  if (!compressed || !*compressed) return;
+  Handle *h = reinterpret_cast<Handle *>(*compressed);
+  if (h->magic != kHandleMagic) { fail(-5, __func__, __LINE__, "invalid handle"); return; }
+  destroy_handle(h);
+  *compressed = nullptr;
+}
+
+void get_compressed_freq(void *compressed, double *f) {
+  clear_status();
+  Handle *h = as_handle(compressed);
+  if (!h || !f) return;
+  memcpy(f, h->h_f.data(), sizeof(double) * h->snps);
+}
+
+int mb200_get_layout(void *compressed, mb200_layout *out) {
+  clear_status();
+  Handle *h = as_handle(compressed);
+  if (!h || !out) return status().code ? status().code : -2;
+  out->snps = h->snps;
+  out->indiv = h->indiv;
+  out->pitch_snp_major = h->pitch_s;
+  out->pitch_indiv_major = h->pitch_i;
+  out->d_snp_major = h->d_snp_major;
+  out->d_indiv_major = h->d_indiv_major;
+  out->d_f = h->d_f;
+  out->d_allele_counts = h->d_counts;
+  out->device = h->device;
+  return 0;
+}
+
+int mb200_download_layout(void *compressed, unsigned char *snp_major, unsigned char *indiv_major,
+                          unsigned long long *allele_counts) {
+  clear_status();
+  Handle *h = as_handle(compressed);
+  if (!h) return status().code;
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  if (snp_major)
+    MB_CUDA(cudaMemcpy(snp_major, h->d_snp_major, (size_t)h->snps * h->pitch_s, cudaMemcpyDeviceToHost));
+  if (indiv_major)
+    MB_CUDA(cudaMemcpy(indiv_major, h->d_indiv_major, (size_t)h->indiv * h->pitch_i, cudaMemcpyDeviceToHost));
+  if (allele_counts)
+    MB_CUDA(cudaMemcpy(allele_counts, h->d_counts, sizeof(unsigned long long) * h->snps, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int mb200_simulate_plink_device(unsigned char *d_plink, long snps, long indiv,
+                                unsigned long long seed) {
+  clear_status();
+  MB_CHECK(simulate_plink(d_plink, snps, indiv, seed, 0));
+  MB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int mb200_crossprod_device(const unsigned char *d_x, long k, long rows, int is_plink_format,
+                           int mode, const double *d_f, int do_scale, double *d_ans) {
+  clear_status();
+  return crossprod_device(d_x, k, rows, is_plink_format, mode, d_f, do_scale, d_ans, 0,
+                          &t_cp_timing);
+}
+
+int mb200_crossprod_last_timing(double out[3]) {
+  out[0] = t_cp_timing.gemm_ms;
+  out[1] = t_cp_timing.epilogue_ms;
+  out[2] = t_cp_timing.executed_ops;
+  return 0;
+}
+
+// host-pointer crossproduct: H2D packed matrix, device pipeline, D2H fp64 result
+static int crossprod_host(const unsigned char *x, int k, int rows, double *ans, int is_plink,
+                          int mode, const double *f, int do_scale) {
+  clear_status();
+  if (!x || !ans || k <= 0 || rows <= 0)
+    return fail(-2, __func__, __LINE__, "bad arguments (k=%d rows=%d)", k, rows) ? 1 : 1;
+  if (select_device() < 0) return 1;
+  const long nb = ceil_div(k, 4);
+  uint8_t *d_x = nullptr;
+  double *d_ans = nullptr, *d_f = nullptr;
+  int rc = 0;
+  cudaError_t e;
+#define X_CUDA(expr)                                                                     \
+  if (!rc && (e = (expr)) != cudaSuccess)                                                 \
+    rc = fail((int)e, __func__, __LINE__, "%s: %s", #expr, cudaGetErrorString(e))
+  X_CUDA(cudaMalloc(&d_x, (size_t)rows * nb));
+  X_CUDA(cudaMalloc(&d_ans, sizeof(double) * rows * rows));
+  X_CUDA(cudaMemcpy(d_x, x, (size_t)rows * nb, cudaMemcpyHostToDevice));
+  if (f && mode) {
+    const long nf = mode == 1 ? k : rows;
+    X_CUDA(cudaMalloc(&d_f, sizeof(double) * nf));
+    X_CUDA(cudaMemcpy(d_f, f, sizeof(double) * nf, cudaMemcpyHostToDevice));
+  }
+  if (!rc) rc = crossprod_device(d_x, k, rows, is_plink, mode, d_f, do_scale, d_ans, 0, &t_cp_timing);
+  X_CUDA(cudaMemcpy(ans, d_ans, sizeof(double) * rows * rows, cudaMemcpyDeviceToHost));
+#undef X_CUDA
+  cudaFree(d_x);
+  cudaFree(d_ans);
+  cudaFree(d_f);
+  return rc ? 1 : 0;
+}
+
+int snp_multiply_gpu(unsigned char *snp_matrix, int snps, int indiv, double *ans,
+                     bool is_plink_format) {
+  return crossprod_host(snp_matrix, snps, indiv, ans, is_plink_format, 0, nullptr, 0);
+}
+int mb200_grm(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool is_plink_format,
+              const double *f, bool do_scale) {
+  return crossprod_host(snp_matrix, snps, indiv, ans, is_plink_format, 1, f, do_scale);
+}
+int mb200_ld(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool is_plink_format,
+             const double *f) {
+  return crossprod_host(snp_matrix, snps, indiv, ans, is_plink_format, 2, f, 0);
+}
+
+}  // extern "C"

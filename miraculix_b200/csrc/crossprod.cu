@@ -1,0 +1,134 @@
+// crossprod.cu -- driver of the crossproduct / GRM / LD path on device-resident input
+// (SURVEY.md 8a rows a9-a13).  Replaces snp_crossproduct (reference
+// src/cuda/snp_multiply_cuda.cu:38-368: per-tile-pair H2D, serialised CUTLASS launches, D2H of
+// int32 tiles, host cast + scatter) and the host BLAS epilogues of grm()/ld()
+// (src/bindings/Julia/crossproduct.jl:91-106, :128-152).
+//
+// Pipeline per call, all on one stream:
+//   for each K-slab:  expand_2bit_kernel (2-bit -> int8)  ->  GEMM  C32 (+)= X8 X8^T  (upper tiles)
+//   counts_to_double_kernel (int32 -> fp64, mirror)  ->  optional GRM / LD epilogue
+#include <stdlib.h>
+#include "common.cuh"
+#include "crossprod_kernels.cuh"
+#include "handle.h"
+
+namespace mb200 {
+
+struct TileCoord;
+int build_tile_list(long rows, TileCoord **d_tiles, int *num_tiles, cudaStream_t stream);
+int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
+                        const TileCoord *d_tiles,
+                        int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
+                        cudaStream_t stream);
+
+static int upload_lut() {
+  uint8_t table[256];
+  host_plink2twobit(table);
+  MB_CUDA(cudaMemcpyToSymbol(c_plink2twobit, table, 256));
+  return 0;
+}
+
+int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
+                     const double *d_f, int do_scale, double *d_ans, cudaStream_t stream,
+                     CrossprodTiming *timing) {
+  if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
+  int device = 0;
+  MB_CUDA(cudaGetDevice(&device));
+  const int sms = device_sm_count(device);
+  const long nb = ceil_div(k, 4);
+  const long rows_pad = round_up(rows, 256);
+
+  // K-slab size: int8 slab of at most MB200_SLAB_GB (default 8) GiB, multiple of 128 columns
+  double slab_gb = 8.0;
+  if (const char *e = getenv("MB200_SLAB_GB")) slab_gb = atof(e) > 0 ? atof(e) : slab_gb;
+  long slab_kbytes = (long)(slab_gb * 1073741824.0 / (double)rows_pad) / 4 / 32 * 32;
+  if (slab_kbytes < 32) slab_kbytes = 32;
+  if (slab_kbytes > round_up(nb, 32)) slab_kbytes = round_up(nb, 32);
+  const long kpad = slab_kbytes * 4;
+
+  if (is_plink_format) MB_CHECK(upload_lut());
+
+  int8_t *X8 = nullptr;
+  int32_t *C32 = nullptr;
+  double *d_m = nullptr;
+  TileCoord *d_tiles = nullptr;
+  int num_tiles = 0;
+  cudaEvent_t e0, e1, e2;
+  MB_CUDA(cudaEventCreate(&e0));
+  MB_CUDA(cudaEventCreate(&e1));
+  MB_CUDA(cudaEventCreate(&e2));
+  MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
+  MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
+  MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
+  const int tc = options().crossprod_mode == 1;
+  if (tc) MB_CHECK(build_tile_list(rows, &d_tiles, &num_tiles, stream));
+
+  MB_CUDA(cudaEventRecord(e0, stream));
+  double executed_ops = 0.0;
+  int slab = 0;
+  for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
+    const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
+    const long kuse = round_up(kbytes * 4, 128);  // columns the GEMM walks this slab
+    // expand zero-fills the whole pitch beyond this slab's bytes; the GEMM walks [0, kuse)
+    expand_2bit_kernel<<<sms * 8, 256, 0, stream>>>(d_x, rows, nb, kb0, kbytes, is_plink_format,
+                                                   X8, rows_pad, kpad);
+    count_launch();
+    MB_LAUNCH_CHECK();
+    if (tc) {
+      MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
+                                   sms, stream));
+      executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
+    } else {
+      const unsigned g = (unsigned)(rows_pad / 64);
+      crossprod_simt_kernel<<<dim3(g, g), 256, 0, stream>>>(X8, kpad, C32, rows_pad, slab > 0);
+      count_launch();
+      MB_LAUNCH_CHECK();
+      executed_ops += 2.0 * 64.0 * 64.0 * (double)kpad * (double)g * (g + 1) / 2.0;
+    }
+  }
+  MB_CUDA(cudaEventRecord(e1, stream));
+
+  const unsigned tb = (unsigned)ceil_div(rows, 32);
+  counts_to_double_kernel<<<dim3(tb, tb), 256, 0, stream>>>(C32, rows_pad, rows, d_ans);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  if (mode == 1) {  // centred (and scaled) GRM
+    colsum_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(d_ans, rows, d_m);
+    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
+    if (do_scale) {
+      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
+      count_launch();
+    }
+    grm_affine_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_m, d_m + rows, do_scale);
+    count_launch(3);
+    MB_LAUNCH_CHECK();
+  } else if (mode == 2) {  // LD: rows = SNPs, k = individuals
+    if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for LD");
+    ld_rank1_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_f, -4.0 * (double)k, d_m);
+    ld_scale_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_m);
+    count_launch(2);
+    MB_LAUNCH_CHECK();
+  }
+  MB_CUDA(cudaEventRecord(e2, stream));
+
+  MB_CUDA(cudaFreeAsync(X8, stream));
+  MB_CUDA(cudaFreeAsync(C32, stream));
+  MB_CUDA(cudaFreeAsync(d_m, stream));
+  if (d_tiles) MB_CUDA(cudaFreeAsync(d_tiles, stream));
+  MB_CUDA(cudaStreamSynchronize(stream));
+  if (timing) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, e0, e1);
+    cudaEventElapsedTime(&b, e1, e2);
+    timing->gemm_ms = a;
+    timing->epilogue_ms = b;
+    timing->executed_ops = executed_ops;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaEventDestroy(e2);
+  return 0;
+}
+
+}  // namespace mb200

@@ -1,0 +1,197 @@
+// crossprod_kernels.cuh -- small HBM-bound kernels around the crossproduct GEMM
+// (SURVEY.md 8a rows a9, a11, a12, a13).
+#pragma once
+#include "common.cuh"
+
+namespace mb200 {
+
+// PLINK -> 2bit byte table, generated on the host at first use by the rule of the reference's
+// generator (src/bindings/Julia/read_plink.jl:50-80): most significant pair first, "10" -> 1,
+// "11" -> 2, any "01" pair turns the whole byte into 0xff.  Equals d_conversion_table
+// (src/cuda/snp_multiply_cuda.h:202); tests/test_golden.py checks all 256 entries.
+__constant__ uint8_t c_plink2twobit[256];
+
+inline void host_plink2twobit(uint8_t *table) {
+  for (int v = 0; v < 256; v++) {
+    uint8_t out = 0;
+    for (int pos = 3; pos >= 0; pos--) {
+      const int c = (v >> (2 * pos)) & 3;
+      out = (uint8_t)(out << 2);
+      if (c == 2) out |= 1;
+      else if (c == 3) out |= 2;
+      else if (c == 1) { out = 0xff; break; }
+    }
+    table[v] = out;
+  }
+}
+
+// Expand K-slab [kb0, kb0 + kbytes) (in packed bytes) of the 2-bit matrix x[rows][nb] to int8
+// X8[rows_pad][kpad] (kpad = 4*kbytes rounded up to 128); every 2-bit field is the value 0..3
+// (replaces the two masked u4 passes of src/cuda/snp_multiply_cuda.h:170-192 and, with
+// is_plink, device_convert_plink_2bit :370-373).  One thread per 4 packed bytes -> 16 B store.
+// Rows >= rows and columns >= 4*kbytes are written as zero.
+__global__ void __launch_bounds__(256)
+expand_2bit_kernel(const uint8_t *__restrict__ x, long rows, long nb, long kb0, long kbytes,
+                   int is_plink, int8_t *__restrict__ X8, long rows_pad, long kpad) {
+  const long groups_per_row = kpad / 16;
+  const long total = rows_pad * groups_per_row;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total;
+       g += (long)gridDim.x * blockDim.x) {
+    const long r = g / groups_per_row, gc = g % groups_per_row;
+    uint32_t out[4] = {0u, 0u, 0u, 0u};
+    if (r < rows) {
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const long b = gc * 4 + t;
+        if (b < kbytes) {
+          uint32_t v = x[r * nb + kb0 + b];
+          if (is_plink) v = c_plink2twobit[v];
+          out[t] = (v & 3u) | ((v & 0xCu) << 6) | ((v & 0x30u) << 12) | ((v & 0xC0u) << 18);
+        }
+      }
+    }
+    *reinterpret_cast<uint4 *>(X8 + r * kpad + gc * 16) = make_uint4(out[0], out[1], out[2], out[3]);
+  }
+}
+
+// int32 counts (row-major, ld32, valid where row <= col) -> fp64 full symmetric column-major
+// n x n (reference host loop src/cuda/snp_multiply_cuda.cu:330-340).  32x32 tiles.
+__global__ void __launch_bounds__(256)
+counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
+                        double *__restrict__ ans) {
+  __shared__ int32_t t[32][33];
+  const long bi = blockIdx.x, bj = blockIdx.y;  // output tile: rows i in bi, cols j in bj
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  if (bi <= bj) {
+    // source M32[i][j], contiguous in j: load (i = ty.., j = tx), transpose through smem
+    for (int yy = ty; yy < 32; yy += 8) {
+      const long i = bi * 32 + yy, j = bj * 32 + tx;
+      t[yy][tx] = (i < n && j < n) ? M32[(i <= j ? i : j) * ld32 + (i <= j ? j : i)] : 0;
+    }
+    __syncthreads();
+    for (int yy = ty; yy < 32; yy += 8) {
+      const long j = bj * 32 + yy, i = bi * 32 + tx;
+      if (i < n && j < n) ans[i + j * n] = (double)t[tx][yy];
+    }
+  } else {
+    // lower tile: value = M32[j][i], contiguous in i -> direct coalesced read and write
+    for (int yy = ty; yy < 32; yy += 8) {
+      const long j = bj * 32 + yy, i = bi * 32 + tx;
+      if (i < n && j < n) ans[i + j * n] = (double)M32[j * ld32 + i];
+    }
+  }
+}
+
+// column sums m_j = sum_i M[i,j] (col_sum of src/bindings/Julia/crossproduct.jl:92); one warp
+// per column, exact while the sums stay below 2^53 (integer-valued doubles).
+__global__ void __launch_bounds__(256)
+colsum_kernel(const double *__restrict__ M, long n, double *__restrict__ m) {
+  const long j = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (j >= n) return;
+  const int lane = threadIdx.x & 31;
+  double acc = 0.0;
+  for (long i = lane; i < n; i += 32) acc += M[i + j * n];
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) m[j] = acc;
+}
+// single-block reductions: total = sum m_j ;  c = 2 sum f (1 - f)
+__global__ void __launch_bounds__(1024)
+reduce_sum_kernel(const double *__restrict__ v, long n, int mode, double *__restrict__ out) {
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (long i = threadIdx.x; i < n; i += 1024) acc += mode ? v[i] * (1.0 - v[i]) : v[i];
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    acc = red[threadIdx.x];
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (threadIdx.x == 0) *out = mode ? 2.0 * acc : acc;
+  }
+}
+// GRM affine epilogue in the order of crossproduct.jl:95-106:
+//   M += (-1/n) m_i ; M += (-1/n) m_j ; M += total/n^2 ; if do_scale M /= c
+// scal[0] = total, scal[1] = c.  No FMA contraction: each step rounds like the BLAS sequence.
+__global__ void __launch_bounds__(256)
+grm_affine_kernel(double *__restrict__ M, long n, const double *__restrict__ m,
+                  const double *__restrict__ scal, int do_scale) {
+  const long total = n * n;
+  const double alpha = -1.0 / (double)n;
+  const double shift = scal[0] / ((double)n * (double)n);
+  const double c = scal[1];
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long)gridDim.x * blockDim.x) {
+    const long i = e % n, j = e / n;
+    double v = M[e];
+    v = __dadd_rn(v, __dmul_rn(alpha, m[i]));
+    v = __dadd_rn(v, __dmul_rn(alpha, m[j]));
+    v = __dadd_rn(v, shift);
+    if (do_scale) v = v / c;
+    M[e] = v;
+  }
+}
+// LD epilogue (crossproduct.jl:128-152): M -= 4 n_obs f_i f_j ; then / sigma_i / sigma_j with
+// sigma = sqrt(diag).  Two passes because the diagonal must be final first.
+__global__ void __launch_bounds__(256)
+ld_rank1_kernel(double *__restrict__ M, long n, const double *__restrict__ f, double alpha,
+                double *__restrict__ sigma) {
+  const long total = n * n;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long)gridDim.x * blockDim.x) {
+    const long i = e % n, j = e / n;
+    // symmetric by construction: use the (min,max) ordering of the syr! upper update
+    const double fi = f[i < j ? i : j], fj = f[i < j ? j : i];
+    const double v = __dadd_rn(M[e], __dmul_rn(__dmul_rn(alpha, fi), fj));
+    M[e] = v;
+    if (i == j) sigma[i] = sqrt(v);
+  }
+}
+__global__ void __launch_bounds__(256)
+ld_scale_kernel(double *__restrict__ M, long n, const double *__restrict__ sigma) {
+  const long total = n * n;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long)gridDim.x * blockDim.x) {
+    const long i = e % n, j = e / n;
+    M[e] = M[e] / sigma[i] / sigma[j];
+  }
+}
+
+// mode 0 fallback GEMM: dp4a SIMT, 64x64 output tile per block, upper-triangle blocks only.
+// C32[i][j] (+)= sum_k X8[i][k] X8[j][k]
+__global__ void __launch_bounds__(256)
+crossprod_simt_kernel(const int8_t *__restrict__ X8, long kpad, int32_t *__restrict__ C32,
+                      long ld32, int accumulate) {
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj < bi) return;
+  __shared__ uint32_t As[64][17], Bs[64][17];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, 4x4 outputs
+  int acc[4][4] = {};
+  for (long k0 = 0; k0 < kpad; k0 += 64) {
+    __syncthreads();
+    for (int e = tid; e < 64 * 16; e += 256) {
+      const int r = e >> 4, w = e & 15;
+      As[r][w] = *reinterpret_cast<const uint32_t *>(X8 + ((long)bi * 64 + r) * kpad + k0 + w * 4);
+      Bs[r][w] = *reinterpret_cast<const uint32_t *>(X8 + ((long)bj * 64 + r) * kpad + k0 + w * 4);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < 16; w++) {
+      uint32_t a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { a[u] = As[ty * 4 + u][w]; b[u] = Bs[tx * 4 + u][w]; }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) acc[u][v] = __dp4a((int)a[u], (int)b[v], acc[u][v]);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 4; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      int32_t *p = C32 + ((long)bi * 64 + ty * 4 + u) * ld32 + (long)bj * 64 + tx * 4 + v;
+      *p = accumulate ? *p + acc[u][v] : acc[u][v];
+    }
+}
+
+}  // namespace mb200

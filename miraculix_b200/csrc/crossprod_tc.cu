@@ -1,0 +1,229 @@
+// crossprod_tc.cu -- the crossproduct GEMM  C32 = X8 X8^T  on 5th-gen tensor cores
+// (SURVEY.md 8a rows a9/a10).
+//
+// Replaces the CUTLASS 2.10 uint4b_t tensor-op GEMM with the custom two-pass
+// mma.sync.m8n8k32.u4 micro-kernel (reference src/cuda/snp_multiply_cuda.cu:123-171,
+// src/cuda/snp_multiply_cuda.h:121-199) and its host-driven tile loop (:190-340).
+// tcgen05 has no 4-bit integer MMA, so the operands are int8 (expanded once per K-slab by
+// expand_2bit_kernel) and the whole upper triangle is one persistent launch:
+//
+//   warp 0      TMA producer   cp.async.bulk.tensor 2-D tiles, 128-byte swizzle, mbarrier ring
+//   warp 1      MMA issuer     tcgen05.mma.cta_group::1.kind::i8, M=128 N=256 K=32, SS operands,
+//                              int32 accumulators in TMEM (2 x 256 columns, double-buffered)
+//   warps 2..5  epilogue       tcgen05.ld 32x32b.x32 -> registers -> int32 global (+= for slabs>0)
+//
+// One CTA per SM, static round-robin over a host-built list of upper-triangle tiles that is
+// ordered in L2-friendly super-blocks.
+#include <cuda.h>
+#include "common.cuh"
+#include "handle.h"
+
+namespace mb200 {
+
+constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 128;  // BK in bytes = int8 elements
+constexpr int TC_STAGES = 4;
+constexpr int TC_A_BYTES = TC_BM * TC_BK;  // 16 KB
+constexpr int TC_B_BYTES = TC_BN * TC_BK;  // 32 KB
+constexpr int TC_STAGE_BYTES = TC_A_BYTES + TC_B_BYTES;
+constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int TC_THREADS = 192;
+
+struct TileCoord {
+  int mi, nj;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                    const __grid_constant__ CUtensorMap tmap_b,
+                    const TileCoord *__restrict__ tiles, int num_tiles, int num_kblocks,
+                    int32_t *__restrict__ C32, long ld32, int accumulate) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                              ~(uintptr_t)1023);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES);
+  uint64_t *full = bars, *empty = bars + TC_STAGES;
+  uint64_t *tfull = bars + 2 * TC_STAGES, *tempty = bars + 2 * TC_STAGES + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * TC_STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TC_STAGES; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; a++) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const TileCoord tc = tiles[t];
+        for (int kb = 0; kb < num_kblocks; kb++) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t *sa = smem + stage * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
+          mbar_expect_tx(&full[stage], TC_STAGE_BYTES);
+          tma_load_2d(sa, &tmap_a, &full[stage], kb * TC_BK, tc.mi * TC_BM);
+          tma_load_2d(sb, &tmap_b, &full[stage], kb * TC_BK, tc.nj * TC_BN);
+          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_i8(TC_BM, TC_BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * TC_BN;
+        for (int kb = 0; kb < num_kblocks; kb++) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * TC_STAGE_BYTES);
+          const uint64_t adesc = make_desc_k_sw128(sa);
+          const uint64_t bdesc = make_desc_k_sw128(sa + TC_A_BYTES);
+#pragma unroll
+          for (int k4 = 0; k4 < TC_BK / 32; k4++)  // +32 bytes along K = +2 in the >>4 address field
+            mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
+          tc_commit(&empty[stage]);
+          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&tfull[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const TileCoord tc = tiles[t];
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const long row = (long)tc.mi * TC_BM + quad * 32 + lane;
+      int32_t *crow = C32 + row * ld32 + (long)tc.nj * TC_BN;
+      const uint32_t taddr = tmem_base + acc * TC_BN + ((uint32_t)(quad * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < TC_BN / 32; c++) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        int4 *dst = reinterpret_cast<int4 *>(crow + c * 32);
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          int4 v = make_int4((int)r[4 * q], (int)r[4 * q + 1], (int)r[4 * q + 2], (int)r[4 * q + 3]);
+          if (accumulate) {
+            const int4 o = dst[q];
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          }
+          dst[q] = v;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                    const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                    const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+// 2-D u8 tensor [rows][row_bytes] (row pitch = pitch bytes), box = box_rows x box_bytes.
+int make_tmap_u8_2d(CUtensorMap *map, const void *base, long row_bytes, long rows, long pitch,
+                    int box_bytes, int box_rows, int swizzle128) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return fail(-10, __func__, __LINE__, "cuTensorMapEncodeTiled not available");
+  cuuint64_t dims[2] = {(cuuint64_t)row_bytes, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch};
+  cuuint32_t box[2] = {(cuuint32_t)box_bytes, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(-11, __func__, __LINE__, "cuTensorMapEncodeTiled -> %d", (int)r);
+  return 0;
+}
+
+// Upper-triangle tile list in super-blocks of 16 x 8 tiles (2048 x 2048 outputs) so that the
+// ~148 tiles in flight share operand panels in L2.
+int build_tile_list(long rows, TileCoord **d_tiles, int *num_tiles, cudaStream_t stream) {
+  const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
+  std::vector<TileCoord> v;
+  for (int sn = 0; sn < Nt; sn += 8)
+    for (int sm = 0; sm < Mt; sm += 16)
+      for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
+        for (int mi = sm; mi < sm + 16 && mi < Mt; mi++)
+          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj});
+  *num_tiles = (int)v.size();
+  MB_CUDA(cudaMallocAsync(d_tiles, sizeof(TileCoord) * v.size(), stream));
+  MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice,
+                          stream));
+  MB_CUDA(cudaStreamSynchronize(stream));  // v goes out of scope
+  return 0;
+}
+
+int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
+                        const TileCoord *d_tiles,
+                        int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
+                        cudaStream_t stream) {
+  MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               TC_SMEM));
+  CUtensorMap ta, tb;
+  MB_CHECK(make_tmap_u8_2d(&ta, X8, kcols, rows_pad, pitch, TC_BK, TC_BM, 1));
+  MB_CHECK(make_tmap_u8_2d(&tb, X8, kcols, rows_pad, pitch, TC_BK, TC_BN, 1));
+  const int grid = num_tiles < sm_count ? num_tiles : sm_count;
+  crossprod_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
+                                                             (int)(kcols / TC_BK), C32, ld32,
+                                                             accumulate);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace mb200

@@ -1,0 +1,72 @@
+// handle.h -- the opaque object behind `void *compressed` and the process-global options.
+// Replaces struct GPU_gemm_storage (reference src/cuda/dgemm_compressed_cuda.h:87-100) and the
+// ten flags of setOptions_compressed that reach the GPU path (src/miraculix/options.h:27-57).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <vector>
+
+namespace mb200 {
+
+struct Options {
+  int use_gpu = 1;
+  int cores = 0;
+  int centered = 1;  // genetics.centered: 1 = RowMeans (subtract 2 f), 0 = raw Z
+  int print_details = 0;
+  int variant = 256;
+  int dgemm_mode = 1;      // 0 fp64 SIMT, 1 int8-slice tcgen05
+  int dgemm_slices = 7;    // 8-bit digits per column of B in mode 1
+  int crossprod_mode = 1;  // 0 dp4a SIMT, 1 tcgen05
+};
+Options &options();
+
+constexpr uint32_t kHandleMagic = 0x4d423230u;  // "MB20"
+
+// HBM layout: both orientations value-coded (2-bit field = genotype 0/1/2, PLINK
+// missing -> 0), rows padded with zeros to a multiple of 128 bytes (= 512 genotypes), base
+// pointers 256-byte aligned (cudaMalloc).
+struct Handle {
+  uint32_t magic = kHandleMagic;
+  int device = 0;
+  long snps = 0, indiv = 0;
+  int max_n = 0;
+  long pitch_s = 0;  // bytes per SNP row   (snp-major:  [snps][pitch_s],  K = indiv)
+  long pitch_i = 0;  // bytes per indiv row (indiv-major:[indiv][pitch_i], K = snps)
+  uint8_t *d_snp_major = nullptr;
+  uint8_t *d_indiv_major = nullptr;
+  double *d_f = nullptr;                   // allele frequencies (caller-supplied), length snps
+  unsigned long long *d_counts = nullptr;  // allele counts per SNP from the repack
+  std::vector<double> h_f;                 // host copy for get_compressed_freq
+  // per-call scratch, sized for max_n columns, allocated once (no per-call malloc):
+  double *d_B = nullptr;   // [max(snps,indiv)] x max_n, ld = rows of B
+  double *d_C = nullptr;   // [max(snps,indiv)] x max_n
+  double *d_w = nullptr;   // centring scalars / column scales, 4*max_n doubles
+  int8_t *d_Bq = nullptr;  // sliced int8 panel for the tensor-core path
+  size_t bq_bytes = 0;
+  void *pinned = nullptr;  // pinned staging for host<->device copies of B / C
+  size_t pinned_bytes = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int sm_count = 148;
+};
+
+Handle *as_handle(void *p);  // validates magic, sets device; nullptr + status on failure
+
+// repack.cu
+int repack_from_device(Handle *h, const uint8_t *d_plink);  // d_plink: [snps][ceil(indiv/4)]
+int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long seed,
+                   cudaStream_t stream);
+int freq_from_counts(Handle *h);  // d_f = counts / (2 indiv)
+
+// dgemm.cu
+int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
+
+// crossprod.cu
+struct CrossprodTiming {
+  double gemm_ms = 0, epilogue_ms = 0, executed_ops = 0;
+};
+int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
+                     const double *d_f, int do_scale, double *d_ans, cudaStream_t stream,
+                     CrossprodTiming *timing);
+
+}  // namespace mb200

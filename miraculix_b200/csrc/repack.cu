@@ -1,0 +1,165 @@
+// repack.cu -- plink2compressed on the GPU.
+//
+// Replaces plink2gpu (reference src/cuda/dgemm_compressed_cuda.cu:43-170), which uploads TWO
+// host-prepared orientations of the bed, and the caller-side host transposes that feed it
+// (src/bindings/Julia/compressed_operations.jl:45-66, src/bindings/Fortran/modplink_miraculix.f90:177-218).
+// Here only the SNP-major bed is read; one kernel writes both device orientations, recodes
+// PLINK codes to genotype values (MXinfo.h:143: 00->0, 01->0, 10->1, 11->2), zero-pads every
+// row to 128 bytes and accumulates the per-SNP allele counts.
+//
+// HBM-bound: algorithmic bytes = snps*ceil(indiv/4) read + snps*pitch_s + indiv*pitch_i written.
+#include "common.cuh"
+#include "handle.h"
+
+namespace mb200 {
+
+constexpr int RP_TILE = 256;         // SNPs per tile = individuals per tile
+constexpr int RP_BYTES = 64;         // input bytes per SNP row of a tile (256 individuals)
+constexpr int RP_PITCH = 68;         // smem row pitch (bytes)
+
+__device__ __forceinline__ uint32_t plink_to_value_byte(uint32_t b) {
+  // per 2-bit field: value = hi + (hi & lo)  ->  value_hi = hi & lo, value_lo = hi & ~lo
+  uint32_t hi = (b >> 1) & 0x55u, lo = b & 0x55u;
+  return ((hi & lo) << 1) | (hi & ~lo);
+}
+
+// plink: rows [s_begin, s_begin + s_count) of the bed, row pitch bs bytes, base = row s_begin.
+__global__ void __launch_bounds__(256)
+repack_kernel(const uint8_t *__restrict__ plink, long s_begin, long s_count, long snps, long indiv,
+              long bs, uint8_t *__restrict__ snp_major, long pitch_s,
+              uint8_t *__restrict__ indiv_major, long pitch_i,
+              unsigned long long *__restrict__ counts) {
+  __shared__ uint8_t tile[RP_TILE * RP_PITCH];
+  const int tid = threadIdx.x;
+  const long i0 = (long)blockIdx.x * RP_TILE;             // first individual of the tile
+  const long sl0 = (long)blockIdx.y * RP_TILE;            // first SNP of the tile, chunk-local
+  const long b0 = i0 >> 2;
+
+  // phase 1: coalesced read of 256 rows x 64 bytes, recode, write SNP-major, stage in smem
+  for (int e = tid; e < RP_TILE * RP_BYTES; e += 256) {
+    const int r = e >> 6, cb = e & 63;
+    const long sl = sl0 + r, gb = b0 + cb;
+    uint32_t v = 0;
+    if (sl < s_count && gb < bs) {
+      v = plink_to_value_byte(plink[sl * bs + gb]);
+      const long keep = indiv - 4 * gb;                   // valid fields in this byte
+      if (keep < 4) v &= (1u << (2 * keep)) - 1u;
+      snp_major[(s_begin + sl) * pitch_s + gb] = (uint8_t)v;
+    }
+    tile[r * RP_PITCH + cb] = (uint8_t)v;
+    // allele count of this half row: a warp covers 32 consecutive bytes of ONE row
+    int cnt = __popc(v & 0x55u) + 2 * __popc(v & 0xAAu);
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if ((tid & 31) == 0 && cnt && sl < s_count)
+      atomicAdd(&counts[s_begin + sl], (unsigned long long)cnt);
+  }
+  __syncthreads();
+
+  // phase 2: each output byte gathers one field from four consecutive SNP rows
+  const long q0 = (s_begin + sl0) >> 2;                   // s_begin, sl0 are multiples of 4
+  const long bi = (snps + 3) >> 2;
+  for (int e = tid; e < RP_TILE * RP_BYTES; e += 256) {
+    const int il = e >> 6, q = e & 63;
+    const long i = i0 + il, gq = q0 + q;
+    if (i < indiv && gq < bi) {
+      const int cb = il >> 2, sh = 2 * (il & 3);
+      const uint8_t *t = tile + (4 * q) * RP_PITCH + cb;
+      uint32_t out = ((t[0] >> sh) & 3u) | (((t[RP_PITCH] >> sh) & 3u) << 2) |
+                     (((t[2 * RP_PITCH] >> sh) & 3u) << 4) | (((t[3 * RP_PITCH] >> sh) & 3u) << 6);
+      indiv_major[i * pitch_i + gq] = (uint8_t)out;
+    }
+  }
+}
+
+int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count) {
+  const long bs = ceil_div(h->indiv, 4);
+  dim3 grid((unsigned)ceil_div(h->indiv, RP_TILE), (unsigned)ceil_div(s_count, RP_TILE));
+  repack_kernel<<<grid, 256, 0, h->stream>>>(d_chunk, s_begin, s_count, h->snps, h->indiv, bs,
+                                             h->d_snp_major, h->pitch_s, h->d_indiv_major,
+                                             h->pitch_i, h->d_counts);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  return 0;
+}
+
+int repack_from_device(Handle *h, const uint8_t *d_plink) {
+  // grid.y limit 65535 tiles = 16.7M SNPs per launch; chunk to stay below
+  const long bs = ceil_div(h->indiv, 4);
+  const long max_rows = 65535L * RP_TILE;
+  for (long s = 0; s < h->snps; s += max_rows) {
+    long cnt = h->snps - s < max_rows ? h->snps - s : max_rows;
+    MB_CHECK(repack_chunk(h, d_plink + s * bs, s, cnt));
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// freq = counts / (2 indiv)  (popcount rule, reference src/bindings/Julia/read_plink.jl:197-203)
+// ---------------------------------------------------------------------------------------------
+__global__ void freq_kernel(const unsigned long long *__restrict__ counts, long snps, double denom,
+                            double *__restrict__ f) {
+  long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < snps) f[j] = (double)counts[j] / denom;
+}
+int freq_from_counts(Handle *h) {
+  freq_kernel<<<(unsigned)ceil_div(h->snps, 256), 256, 0, h->stream>>>(
+      h->d_counts, h->snps, 2.0 * (double)h->indiv, h->d_f);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// On-device simulator (benchmark inputs): p_j ~ U(0.1,0.6),
+// z_ij ~ Binomial(2,p_j) = [u1<p] + [u2<p], PLINK codes 0->00, 1->10, 2->11, pad bits 00.
+// Counter-based: every genotype is a pure function of (seed, snp, indiv).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {  // splitmix64 finaliser
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void __launch_bounds__(256)
+simulate_kernel(uint8_t *__restrict__ plink, long snps, long indiv, long bs,
+                unsigned long long seed) {
+  const long total_words = snps * ((bs + 3) / 4);
+  const long wpr = (bs + 3) / 4;  // 32-bit words per row (last one partial)
+  for (long w = (long)blockIdx.x * blockDim.x + threadIdx.x; w < total_words;
+       w += (long)gridDim.x * blockDim.x) {
+    const long s = w / wpr, wb = w % wpr;
+    const uint64_t ks = mix64(seed ^ (0xA5A5A5A5ull + (uint64_t)s * 0x100000001B3ull));
+    const uint32_t thr = (uint32_t)((0.1 + 0.5 * ((ks >> 11) * (1.0 / 9007199254740992.0))) *
+                                    4294967296.0);
+    uint32_t word = 0;
+#pragma unroll
+    for (int g = 0; g < 16; g += 2) {  // one 64-bit hash -> two genotypes
+      const long i = wb * 16 + g;
+      uint64_t r = mix64(ks + (uint64_t)i * 0xD6E8FEB86659FD93ull);
+      uint32_t a0 = (uint32_t)r < thr, a1 = (uint32_t)(r >> 32) < thr;
+      r = mix64(r);
+      uint32_t c0 = (uint32_t)r < thr, c1 = (uint32_t)(r >> 32) < thr;
+      uint32_t z0 = a0 + a1, z1 = c0 + c1;
+      uint32_t code0 = i < indiv ? (z0 == 0 ? 0u : z0 + 1u) : 0u;
+      uint32_t code1 = (i + 1) < indiv ? (z1 == 0 ? 0u : z1 + 1u) : 0u;
+      word |= (code0 << (2 * g)) | (code1 << (2 * g + 2));
+    }
+    uint8_t *dst = plink + s * bs + wb * 4;
+    const long rem = bs - wb * 4;
+    if (rem >= 4 && ((s * bs) & 3) == 0) {
+      *reinterpret_cast<uint32_t *>(dst) = word;
+    } else {
+      for (int t = 0; t < 4 && t < rem; t++) dst[t] = (uint8_t)(word >> (8 * t));
+    }
+  }
+}
+int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long seed,
+                   cudaStream_t stream) {
+  const long bs = ceil_div(indiv, 4);
+  simulate_kernel<<<148 * 8, 256, 0, stream>>>(d_plink, snps, indiv, bs, seed);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace mb200

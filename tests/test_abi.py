@@ -1,0 +1,92 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/miraculix_b200.h declares, and keeps the reference's error conventions.  No compute
+call needs a GPU here."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "miraculix_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\([^;{]*\)\s*;", src)))
+
+
+def test_header_declares_reference_surface():
+    names = declared_symbols()
+    for ref_name in ("setOptions_compressed", "plink2compressed", "dgemm_compressed",
+                     "free_compressed", "get_compressed_freq", "snp_multiply_gpu"):
+        assert ref_name in names
+
+
+def test_library_exports_every_declared_symbol(lib):
+    from miraculix_b200 import api
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in the header but not exported"
+        assert n in api.SIGNATURES, f"{n} has no ctypes signature in api.SIGNATURES"
+
+
+def _run(code: str):
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    return subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
+                          timeout=300)
+
+
+def test_bad_trans_exits_99(lib):
+    """5codesAPI.c:73-77: anything but N/n/T/t/Y/y -> exit(99)."""
+    r = _run("from miraculix_b200 import api; import ctypes as C; L = api.load_library();"
+             "L.dgemm_compressed(b'X', None, 1, None, 1, None, 1)")
+    assert r.returncode == 99
+
+
+def test_inadmissible_gpu_options_exit_failure(lib):
+    """5codesChar.cc:192-193: gpu needs external freq, ignore_missings, no normalising."""
+    for flags in ("1,0,0,0,1,0,0,1,0,0",   # use_miraculix_freq = 1
+                  "1,0,0,0,0,0,0,0,0,0",   # ignore_missings = 0
+                  "1,0,0,0,1,0,1,0,0,0"):  # do_normalize = 1
+        r = _run(f"from miraculix_b200 import api; api.load_library().setOptions_compressed({flags})")
+        assert r.returncode == 1, flags
+        assert "Fortran frequency" in r.stderr
+    r = _run("from miraculix_b200 import api; api.set_options(use_gpu=True, not_center=True)")
+    assert r.returncode == 0
+
+
+def test_invalid_handle_is_reported_not_crashed(lib):
+    from miraculix_b200 import api
+    buf = np.zeros(4)
+    lib.dgemm_compressed(b"N", None, 1, buf.ctypes.data, 4, buf.ctypes.data, 4)
+    assert lib.mb200_last_status() != 0
+    assert b"invalid" in lib.mb200_last_message()
+    lib.free_compressed(None)  # NULL is a no-op
+
+
+def test_host_argument_checks():
+    from miraculix_b200 import api
+    with pytest.raises(ValueError):
+        api.init_compressed(np.zeros((3, 3), np.uint8), 3, 8, np.zeros(3), 1)  # wrong bed shape
+    with pytest.raises(ValueError):
+        api.grm(np.zeros((4, 2), np.uint8), 8, 4, do_scale=True, allele_freq=np.zeros(3))
+    with pytest.raises(ValueError):
+        api.snp_crossprod(np.zeros((4, 3), np.uint8), 8, 4, is_snpmajor=False)
+
+
+def test_no_device_fails_loudly(lib):
+    """On a box without a GPU the product must error, never fall back to a CPU path."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from miraculix_b200 import api
+    plink = np.zeros((4, 1), np.uint8)
+    with pytest.raises(api.MiraculixError):
+        api.init_compressed(plink, 4, 4, np.zeros(4), 1)
+    with pytest.raises(api.MiraculixError):
+        api.snp_crossprod(np.zeros((4, 1), np.uint8), 4, 4, is_snpmajor=False)

@@ -1,0 +1,129 @@
+"""CPU tests: pin the oracle (oracle/oracle.c) against the reference's golden vectors.
+
+Golden fixtures (tests/golden/, made by make_golden.py from the reference itself):
+  * plink2twobit_lut.npy  = d_conversion_table of src/cuda/snp_multiply_cuda.h:202
+  * dgemm_*.npz           = outputs of the unmodified reference CPU 5codes library
+Procedures re-expressed from the reference's tests: tests/dgemm_compressed/test.jl:97-104
+(dense product on the decompressed matrix), tests/crossproduct/test_grm.jl:127-139 (raw counts
+exact, centred GRM vs BLAS).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cport, ref, simulate
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+TOL = 1e-10  # north-star tolerance for fp64 outputs: max|dC| / max|C|
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def test_lut_matches_reference_table():
+    gold = np.load(os.path.join(GOLDEN, "plink2twobit_lut.npy"))
+    assert np.array_equal(cport.plink2twobit_lut(), gold)
+    # spot values spelled out in the reference table
+    assert gold[0b00000000] == 0 and gold[0b00000010] == 1 and gold[0b00000011] == 2
+    assert gold[0b00000001] == 0xFF and gold[0b11111111] == 0xAA
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "dgemm_*.npz"))))
+def test_oracle_dgemm_matches_reference_outputs(path):
+    g = np.load(path)
+    centered = path.endswith("_c1.npz")
+    snps, indiv = int(g["snps"]), int(g["indiv"])
+    for tr in "NT":
+        C = cport.dgemm_compressed(tr, g["plink"], snps, indiv, g["f"], g[f"B_{tr}"], centered)
+        assert relerr(C, g[f"C_{tr}"]) <= TOL, (path, tr)
+
+
+def test_oracle_dgemm_matches_dense_numpy():
+    snps, indiv = 317, 129
+    plink, Z, f = simulate.simulate(snps, indiv, seed=7, missing=0.02)
+    rng = np.random.default_rng(8)
+    Zc = Z.astype(np.float64) - 2.0 * f[None, :]
+    B = rng.standard_normal((snps, 3))
+    assert relerr(cport.dgemm_compressed("N", plink, snps, indiv, f, B), Zc @ B) < 1e-13
+    B = rng.standard_normal((indiv, 4))
+    assert relerr(cport.dgemm_compressed("T", plink, snps, indiv, f, B), Zc.T @ B) < 1e-13
+    assert relerr(cport.dgemm_compressed("T", plink, snps, indiv, f, B, centered=False),
+                  Z.T.astype(np.float64) @ B) < 1e-13
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/ref_miraculix.so not built")
+def test_oracle_matches_live_reference_library():
+    snps, indiv = 2051, 333
+    plink, Z, f = simulate.simulate(snps, indiv, seed=11, missing=0.01)
+    ref.set_options(cores=4, centered=True)
+    h = ref.RefCompressed(plink, snps, indiv, f, 7)
+    rng = np.random.default_rng(12)
+    for tr, k in (("N", snps), ("T", indiv)):
+        B = np.asfortranarray(rng.standard_normal((k, 7)))
+        assert relerr(cport.dgemm_compressed(tr, plink, snps, indiv, f, B), h.dgemm(tr, B)) <= TOL
+
+
+@pytest.mark.parametrize("snps,indiv", [(1, 1), (5, 3), (64, 64), (1003, 203), (513, 1025)])
+def test_repack_restatement(snps, indiv):
+    plink, Z, _ = simulate.simulate(snps, indiv, seed=snps + indiv, missing=0.05)
+    sm, im = cport.repack(plink, snps, indiv)
+    assert sm.shape[1] % 128 == 0 and im.shape[1] % 128 == 0
+    # round trip: decode(device layout) == decode(bed), element-wise
+    assert np.array_equal(simulate.unpack_2bit(im, snps), Z)
+    assert np.array_equal(simulate.unpack_2bit(sm, indiv), Z.T)
+    # padding is zero
+    assert not simulate.unpack_2bit(im, im.shape[1] * 4)[:, snps:].any()
+    assert not simulate.unpack_2bit(sm, sm.shape[1] * 4)[:, indiv:].any()
+    # transposing twice gives the original (tests/dgemm_compressed/test.jl:79-83)
+    t = cport.transpose_2bit(plink, snps, indiv)
+    assert np.array_equal(cport.transpose_2bit(t, indiv, snps), plink)
+    assert np.array_equal(cport.allele_counts(plink, snps, indiv), Z.sum(axis=0))
+
+
+@pytest.mark.parametrize("snps,indiv", [(953, 752), (200, 37)])
+def test_crossprod_exact(snps, indiv):
+    """test_grm.jl:127-131: raw counts must be exact."""
+    _, Z, _ = simulate.simulate(snps, indiv, seed=3)
+    tb = simulate.pack_2bit(Z)
+    M = cport.crossprod(tb, snps, indiv)
+    want = Z.astype(np.int64) @ Z.T.astype(np.int64)
+    assert np.array_equal(M, want.astype(np.float64))
+    assert np.array_equal(M, M.T)
+
+
+def test_crossprod_plink_format_quirk():
+    """With is_plink_format a byte holding a missing code becomes 0xff = four 3s
+    (src/cuda/snp_multiply_cuda.h:202), exactly as the reference computes it."""
+    snps, indiv = 64, 9
+    plink, Z, _ = simulate.simulate(snps, indiv, seed=5, missing=0.1)
+    codes = simulate.unpack_2bit(plink, indiv).T  # (indiv, snps) PLINK codes
+    x = simulate.pack_2bit(codes)                  # individual-major PLINK-coded
+    lut = np.load(os.path.join(GOLDEN, "plink2twobit_lut.npy"))
+    vals = simulate.unpack_2bit(lut[x], x.shape[1] * 4).astype(np.int64)
+    assert np.array_equal(cport.crossprod(x, snps, indiv, True), (vals @ vals.T).astype(np.float64))
+
+
+def test_grm_epilogue_matches_formula():
+    """docs/grm.md:3-10: G = P Z Z^T P / (2 sum f(1-f)), P = I - 11^T/n."""
+    snps, indiv = 400, 57
+    _, Z, f = simulate.simulate(snps, indiv, seed=9)
+    M = (Z.astype(np.int64) @ Z.T.astype(np.int64)).astype(np.float64)
+    G = cport.grm_epilogue(M, f, True)
+    P = np.eye(indiv) - np.ones((indiv, indiv)) / indiv
+    want = P @ M @ P / (2.0 * np.sum(f * (1.0 - f)))
+    assert relerr(G, want) < 1e-12
+    # centred via allele freq of the data: equals (Z-2f)(Z-2f)^T scaled (test_grm.jl:133-139)
+    Zc = Z - 2.0 * f[None, :]
+    assert relerr(G, Zc @ Zc.T / (2.0 * np.sum(f * (1.0 - f)))) < 1e-10
+
+
+def test_ld_epilogue_is_correlation():
+    snps, indiv = 40, 500
+    _, Z, f = simulate.simulate(snps, indiv, seed=10)
+    M = (Z.T.astype(np.int64) @ Z.astype(np.int64)).astype(np.float64)
+    R = cport.ld_epilogue(M, indiv, f)
+    want = np.corrcoef(Z.T.astype(np.float64))
+    assert relerr(R, want) < 1e-10
