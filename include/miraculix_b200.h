@@ -91,6 +91,9 @@ int mb200_set_crossprod_mode(int mode);
 int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
                                   double *dC, long ldc);
 void *mb200_stream(void *compressed); /* cudaStream_t */
+/* Device time of the MAIN kernel of the last dgemm_compressed call on this handle (CUDA events
+ * recorded on the handle's stream around that one launch); synchronises the stream. */
+int mb200_dgemm_last_kernel_ms(void *compressed, float *ms);
 int mb200_sync(void *compressed);
 
 /* Build a handle from a bed payload that already lives on the device (same layout as the

@@ -327,6 +327,13 @@ void *mb200_stream(void *compressed) {
   Handle *h = as_handle(compressed);
   return h ? (void *)h->stream : nullptr;
 }
+int mb200_dgemm_last_kernel_ms(void *compressed, float *ms) {
+  Handle *h = as_handle(compressed);
+  if (!h || !ms) return status().code ? status().code : -2;
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  MB_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return 0;
+}
 int mb200_sync(void *compressed) {
   Handle *h = as_handle(compressed);
   if (!h) return status().code;

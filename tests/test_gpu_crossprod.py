@@ -1,0 +1,147 @@
+"""GPU parity tests for the crossproduct / GRM / LD path, through the C-ABI.
+
+Bars: integer counts bit-exact; centred GRM and LD max rel. error <= 1e-10 against the oracle's
+restatement of src/bindings/Julia/crossproduct.jl.  Shapes re-express
+tests/crossproduct/test_grm.jl:114-157 (random 0/1/2 matrices, "uneven" dimensions
+snps in {953, 10251} x indiv in {752, 5343}).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cport, simulate
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+TOL = 1e-10
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def exact_counts(vals):
+    """Z Z^T via fp64 BLAS: exact while entries stay below 2^53 (test_grm.jl uses BLAS.gemm)."""
+    v = vals.astype(np.float64)
+    return v @ v.T
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("snps,indiv", [(953, 752), (64, 5), (129, 257), (2051, 1343),
+                                        (10251, 5343)])
+def test_counts_bit_exact(gpu_lib, snps, indiv, mode):
+    from miraculix_b200 import api
+    if mode == 0 and snps * indiv > 4e6:
+        pytest.skip("SIMT cross-check only on the small shapes")
+    _, Z, _ = simulate.simulate(snps, indiv, seed=snps)
+    x = simulate.pack_2bit(Z)
+    gpu_lib.mb200_set_crossprod_mode(mode)
+    try:
+        M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False)
+    finally:
+        gpu_lib.mb200_set_crossprod_mode(1)
+    assert np.array_equal(M, M.T)  # crossproduct.jl:61
+    if snps * indiv <= 4e6:
+        assert np.array_equal(M, cport.crossprod(x, snps, indiv))
+    assert np.array_equal(M, exact_counts(Z))
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_plink_format_table_and_missing_quirk(gpu_lib, mode):
+    """is_plink_format=True: bytes go through the reference table; a byte with a missing code
+    counts as four 3s, exactly like the reference."""
+    from miraculix_b200 import api
+    snps, indiv = 777, 130
+    plink, Z, _ = simulate.simulate(snps, indiv, seed=2, missing=0.03)
+    codes = simulate.unpack_2bit(plink, indiv).T
+    x = simulate.pack_2bit(codes)  # individual-major, PLINK-coded
+    gpu_lib.mb200_set_crossprod_mode(mode)
+    try:
+        M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False, is_plink_format=True)
+    finally:
+        gpu_lib.mb200_set_crossprod_mode(1)
+    assert np.array_equal(M, cport.crossprod(x, snps, indiv, True))
+    lut = np.load(os.path.join(GOLDEN, "plink2twobit_lut.npy"))
+    vals = simulate.unpack_2bit(lut[x], x.shape[1] * 4)
+    assert np.array_equal(M, exact_counts(vals))
+
+
+def test_k_slabs_accumulate_exactly(gpu_lib, monkeypatch):
+    """Force several K-slabs (int32 += epilogue) and compare with the single-slab result."""
+    from miraculix_b200 import api
+    snps, indiv = 5000, 600
+    _, Z, _ = simulate.simulate(snps, indiv, seed=4)
+    x = simulate.pack_2bit(Z)
+    monkeypatch.setenv("MB200_SLAB_GB", "0.0005")  # ~0.5 MB of int8 per slab -> many slabs
+    M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False)
+    assert np.array_equal(M, exact_counts(Z))
+
+
+@pytest.mark.parametrize("snps,indiv", [(953, 752), (3001, 1025)])
+def test_grm_matches_oracle(gpu_lib, snps, indiv):
+    from miraculix_b200 import api
+    _, Z, f = simulate.simulate(snps, indiv, seed=indiv)
+    x = simulate.pack_2bit(Z)
+    counts = cport.crossprod(x, snps, indiv)
+    for do_scale in (True, False):
+        G = api.grm(x, snps, indiv, do_scale=do_scale, allele_freq=f)
+        assert relerr(G, cport.grm_epilogue(counts, f, do_scale)) <= TOL
+        assert relerr(G, G.T) <= 1e-14
+    # test_grm.jl:133-139: equals the centred dense product
+    Zc = Z - 2.0 * f[None, :]
+    G = api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
+    assert relerr(G, Zc @ Zc.T / (2.0 * np.sum(f * (1.0 - f)))) <= 1e-9
+
+
+def test_ld_matches_oracle(gpu_lib):
+    from miraculix_b200 import api
+    snps, indiv = 600, 2000
+    plink, Z, f = simulate.simulate(snps, indiv, seed=6)
+    x = simulate.pack_2bit(Z.T)  # SNP-major twobit
+    R = api.ld(x, snps, indiv, allele_freq=f)
+    counts = cport.crossprod(x, indiv, snps)
+    assert relerr(R, cport.ld_epilogue(counts, indiv, f)) <= TOL
+    assert relerr(R, np.corrcoef(Z.T.astype(np.float64))) <= 1e-9
+
+
+def test_grm_properties_full_size(gpu_lib):
+    """BASELINE config 2 (50k SNPs x 10k individuals): size-independent checks --
+    symmetry, diagonal = sum z^2, sampled entries against direct dot products, and the row sums
+    M 1 = Z (Z^T 1) computed independently by dgemm_compressed."""
+    import ctypes as C
+    import torch
+    from miraculix_b200 import api
+    snps, indiv = 50000, 10000
+    bs = (indiv + 3) // 4
+    d_plink = torch.zeros(snps * bs, dtype=torch.uint8, device="cuda")
+    assert gpu_lib.mb200_simulate_plink_device(d_plink.data_ptr(), snps, indiv, 2) == 0
+    h = C.c_void_p(None)
+    assert gpu_lib.mb200_plink2compressed_device(d_plink.data_ptr(), snps, indiv, None, 1,
+                                                 C.byref(h)) == 0
+    try:
+        lay = api.get_layout(h)
+        d_ans = torch.empty(indiv * indiv, dtype=torch.float64, device="cuda")
+        # the handle's individual-major layout is value-coded 2-bit with a 128-byte pitch: view it
+        # as a (indiv x 4*pitch) twobit matrix (padding fields are zero)
+        rc = gpu_lib.mb200_crossprod_device(lay.d_indiv_major, lay.pitch_indiv_major * 4, indiv, 0,
+                                            0, None, 0, d_ans.data_ptr())
+        assert rc == 0
+        M = d_ans.view(indiv, indiv)
+        assert torch.equal(M, M.T)
+        _, im, cnt = api.download_layout(h)
+        rng = np.random.default_rng(0)
+        rows = rng.integers(0, indiv, size=24)
+        Zs = simulate.unpack_2bit(im[rows], snps).astype(np.int64)
+        sub = M[torch.as_tensor(rows, device="cuda")][:, torch.as_tensor(rows, device="cuda")]
+        assert np.array_equal(sub.cpu().numpy(), (Zs @ Zs.T).astype(np.float64))
+        # row sums through the other kernel family (uncentred dgemm_compressed)
+        api.set_options(use_gpu=True, not_center=True)
+        ones = np.ones((indiv, 1))
+        zt1 = api.dgemm_compressed("T", h, ones, snps, indiv)
+        assert np.array_equal(zt1[:, 0], cnt.astype(np.float64))
+        m = api.dgemm_compressed("N", h, zt1, snps, indiv)[:, 0]
+        assert np.array_equal(M.sum(dim=0).cpu().numpy(), m)
+    finally:
+        api.set_options(use_gpu=True, not_center=False)
+        api.free_compressed(h)

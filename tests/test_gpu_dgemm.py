@@ -1,0 +1,183 @@
+"""GPU parity tests for plink2compressed (repack) and dgemm_compressed, through the C-ABI.
+
+Bars (BASELINE.json north_star): repack bit-exact; fp64 dgemm_compressed max|dC|/max|C| <= 1e-10
+against the reference's own CPU implementation (golden outputs in tests/golden/) and against the
+oracle on seeded inputs.  Shapes follow the reference's tests: tests/dgemm_compressed/test.jl
+(ncol=10, randn B), test_5codesapi.f90 / test_5codesapi_t.f90 (B = -(10 i + j), -(1000 i + j)).
+"""
+import ctypes as C
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cport, simulate
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+TOL = 1e-10
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.fixture(autouse=True)
+def _centered(gpu_lib):
+    from miraculix_b200 import api
+    api.set_options(use_gpu=True, not_center=False)
+    yield
+
+
+@pytest.mark.parametrize("snps,indiv,missing", [(1, 1, 0.0), (5, 3, 0.0), (256, 256, 0.0),
+                                                (1003, 203, 0.02), (513, 1025, 0.05),
+                                                (10000, 1000, 0.0), (300, 4099, 0.01)])
+def test_repack_bit_exact(gpu_lib, snps, indiv, missing):
+    from miraculix_b200 import api
+    plink, Z, f = simulate.simulate(snps, indiv, seed=snps * 7 + indiv, missing=missing)
+    h = api.init_compressed(plink, snps, indiv, f, 1)
+    try:
+        sm, im, cnt = api.download_layout(h)
+        sm_o, im_o = cport.repack(plink, snps, indiv)
+        assert sm.shape == sm_o.shape and im.shape == im_o.shape
+        assert np.array_equal(sm, sm_o)
+        assert np.array_equal(im, im_o)
+        assert np.array_equal(cnt.astype(np.int64), cport.allele_counts(plink, snps, indiv))
+        # round trip against the bed itself
+        assert np.array_equal(simulate.unpack_2bit(im, snps), Z)
+        assert np.array_equal(api.get_compressed_freq(h, snps), f)
+    finally:
+        api.free_compressed(h)
+    assert not h.value  # free_compressed nulls the caller's pointer
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "dgemm_*.npz"))))
+def test_dgemm_matches_reference_golden(gpu_lib, path, mode):
+    """Outputs of the unmodified reference CPU 5codes library on the same inputs."""
+    from miraculix_b200 import api
+    g = np.load(path)
+    centered = path.endswith("_c1.npz")
+    snps, indiv = int(g["snps"]), int(g["indiv"])
+    api.set_options(use_gpu=True, not_center=not centered)
+    gpu_lib.mb200_set_dgemm_mode(mode, 7)
+    h = api.init_compressed(g["plink"], snps, indiv, g["f"], 16)
+    try:
+        for tr in "NT":
+            Cg = api.dgemm_compressed(tr, h, g[f"B_{tr}"], snps, indiv)
+            assert relerr(Cg, g[f"C_{tr}"]) <= TOL, (os.path.basename(path), tr, mode)
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_dgemm_mode(1, 7)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("snps,indiv,ncol", [(10000, 1000, 1), (1003, 203, 10), (2051, 777, 3),
+                                             (512, 128, 16), (4097, 2050, 7)])
+def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode):
+    from miraculix_b200 import api
+    plink, Z, f = simulate.simulate(snps, indiv, seed=snps + ncol, missing=0.01)
+    rng = np.random.default_rng(ncol)
+    gpu_lib.mb200_set_dgemm_mode(mode, 7)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    try:
+        for tr, k in (("N", snps), ("T", indiv)):
+            B = np.asfortranarray(rng.standard_normal((k, ncol)))
+            want = cport.dgemm_compressed(tr, plink, snps, indiv, f, B, True)
+            assert relerr(api.dgemm_compressed(tr, h, B, snps, indiv), want) <= TOL, (tr, mode)
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_dgemm_mode(1, 7)
+
+
+def test_dgemm_leading_dimensions_and_max_n(gpu_lib):
+    """Ldb/Ldc are honoured (reference GPU path ignores them) and n > max_n is refused."""
+    from miraculix_b200 import api
+    snps, indiv, n = 700, 300, 4
+    plink, Z, f = simulate.simulate(snps, indiv, seed=1)
+    rng = np.random.default_rng(2)
+    h = api.init_compressed(plink, snps, indiv, f, n)
+    try:
+        ldb, ldc = snps + 13, indiv + 5
+        Bbig = np.asfortranarray(rng.standard_normal((ldb, n)))
+        Cbig = np.full((ldc, n), 777.0, order="F")
+        gpu_lib.dgemm_compressed(b"n", h, n, Bbig.ctypes.data, ldb, Cbig.ctypes.data, ldc)
+        assert gpu_lib.mb200_last_status() == 0
+        want = cport.dgemm_compressed("N", plink, snps, indiv, f, Bbig[:snps], True)
+        assert relerr(Cbig[:indiv], want) <= TOL
+        assert np.all(Cbig[indiv:] == 777.0)  # rows beyond m untouched
+        # 'y' is an alias of 'T' (5codesAPI.c:73-77)
+        B = np.asfortranarray(rng.standard_normal((indiv, 2)))
+        Cy = np.zeros((snps, 2), order="F")
+        gpu_lib.dgemm_compressed(b"y", h, 2, B.ctypes.data, indiv, Cy.ctypes.data, snps)
+        assert relerr(Cy, cport.dgemm_compressed("T", plink, snps, indiv, f, B, True)) <= TOL
+        # n > max_n
+        B5 = np.asfortranarray(rng.standard_normal((snps, n + 1)))
+        C5 = np.zeros((indiv, n + 1), order="F")
+        gpu_lib.dgemm_compressed(b"N", h, n + 1, B5.ctypes.data, snps, C5.ctypes.data, indiv)
+        assert gpu_lib.mb200_last_status() != 0 and not C5.any()
+    finally:
+        api.free_compressed(h)
+
+
+def test_dgemm_linearity_and_transpose_identity_large(gpu_lib):
+    """Size-independent properties at a size the oracle does not finish in seconds:
+    linearity in B, and <u, A v> == <A^T u, v> for A = Z - 2 1 f^T."""
+    from miraculix_b200 import api
+    snps, indiv = 60000, 8000
+    plink, _, f = simulate.simulate(snps, indiv, seed=42)
+    rng = np.random.default_rng(43)
+    h = api.init_compressed(plink, snps, indiv, f, 2)
+    try:
+        v1, v2 = rng.standard_normal((snps, 1)), rng.standard_normal((snps, 1))
+        a1 = api.dgemm_compressed("N", h, v1, snps, indiv)
+        a2 = api.dgemm_compressed("N", h, v2, snps, indiv)
+        a12 = api.dgemm_compressed("N", h, 2.0 * v1 - 3.0 * v2, snps, indiv)
+        assert relerr(a12, 2.0 * a1 - 3.0 * a2) <= 1e-9
+        u = rng.standard_normal((indiv, 1))
+        atu = api.dgemm_compressed("T", h, u, snps, indiv)
+        lhs, rhs = float(u.T @ a1), float(atu.T @ v1)
+        assert abs(lhs - rhs) <= 1e-9 * max(abs(lhs), np.linalg.norm(u) * np.linalg.norm(a1))
+        # two columns at once == two single calls
+        both = api.dgemm_compressed("N", h, np.hstack([v1, v2]), snps, indiv)
+        assert relerr(both, np.hstack([a1, a2])) <= 1e-12
+    finally:
+        api.free_compressed(h)
+
+
+def test_device_pointer_entry_and_simulator(gpu_lib):
+    """mb200_plink2compressed_device + mb200_dgemm_compressed_device on torch device buffers; the
+    on-device simulator output is a valid bed (no missing codes, zero pad bits) and is
+    deterministic in (seed)."""
+    import torch
+    from miraculix_b200 import api
+    snps, indiv, n = 3000, 1001, 3
+    bs = (indiv + 3) // 4
+    d_plink = torch.zeros(snps * bs, dtype=torch.uint8, device="cuda")
+    assert gpu_lib.mb200_simulate_plink_device(d_plink.data_ptr(), snps, indiv, 5) == 0
+    d2 = torch.zeros_like(d_plink)
+    assert gpu_lib.mb200_simulate_plink_device(d2.data_ptr(), snps, indiv, 5) == 0
+    assert torch.equal(d_plink, d2)
+    plink = d_plink.cpu().numpy().reshape(snps, bs)
+    codes = simulate.unpack_2bit(plink, bs * 4)
+    assert not (codes == 1).any() and not codes[:, indiv:].any()
+    Z = simulate.plink_decode(codes[:, :indiv]).T
+    p = Z.mean(axis=0) / 2.0
+    assert 0.08 < p.min() and p.max() < 0.62 and abs(p.mean() - 0.35) < 0.02
+    h = C.c_void_p(None)
+    assert gpu_lib.mb200_plink2compressed_device(d_plink.data_ptr(), snps, indiv, None, n,
+                                                 C.byref(h)) == 0
+    try:
+        f = api.get_compressed_freq(h, snps)
+        assert np.allclose(f, p, rtol=0, atol=1e-15)
+        B = torch.randn(n, snps, dtype=torch.float64, device="cuda")  # = column-major snps x n
+        Cd = torch.empty(n, indiv, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        assert gpu_lib.mb200_dgemm_compressed_device(0, h, n, B.data_ptr(), snps, Cd.data_ptr(),
+                                                     indiv) == 0
+        assert gpu_lib.mb200_sync(h) == 0
+        want = cport.dgemm_compressed("N", plink, snps, indiv, f, B.cpu().numpy().T, True)
+        assert relerr(Cd.cpu().numpy().T, want) <= TOL
+    finally:
+        api.free_compressed(h)
