@@ -94,6 +94,10 @@ void *mb200_stream(void *compressed); /* cudaStream_t */
 /* Device time of the MAIN kernel of the last dgemm_compressed call on this handle (CUDA events
  * recorded on the handle's stream around that one launch); synchronises the stream. */
 int mb200_dgemm_last_kernel_ms(void *compressed, float *ms);
+/* Durations (ms) of the main kernel of the `last` most recent dgemm_compressed calls on this
+ * handle, oldest first (at most 128 are kept); trans[j] (optional) = direction of call j.
+ * Synchronises the stream.  Returns the number of entries written, or a negative status. */
+int mb200_dgemm_kernel_times(void *compressed, int last, float *ms, int *trans);
 int mb200_sync(void *compressed);
 
 /* Build a handle from a bed payload that already lives on the device (same layout as the

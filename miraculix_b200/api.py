@@ -46,6 +46,8 @@ SIGNATURES = {
     "mb200_stream": (C.c_void_p, [C.c_void_p]),
     "mb200_sync": (C.c_int, [C.c_void_p]),
     "mb200_dgemm_last_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "mb200_dgemm_kernel_times": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float),
+                                           C.POINTER(C.c_int)]),
     "mb200_plink2compressed_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_void_p, C.c_int,
                                                 C.POINTER(C.c_void_p)]),
     "mb200_get_layout": (C.c_int, [C.c_void_p, C.POINTER(Layout)]),

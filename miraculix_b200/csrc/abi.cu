@@ -123,8 +123,10 @@ static void destroy_handle(Handle *h) {
   cudaFree(h->d_w);
   cudaFree(h->d_Bq);
   if (h->pinned) cudaFreeHost(h->pinned);
-  if (h->ev0) cudaEventDestroy(h->ev0);
-  if (h->ev1) cudaEventDestroy(h->ev1);
+  for (int i = 0; i < Handle::kEvRing; i++) {
+    if (h->ev_begin[i]) cudaEventDestroy(h->ev_begin[i]);
+    if (h->ev_end[i]) cudaEventDestroy(h->ev_end[i]);
+  }
   if (h->stream) cudaStreamDestroy(h->stream);
   h->magic = 0;
   delete h;
@@ -157,8 +159,10 @@ static int create_handle(long snps, long indiv, int max_n, Handle **out) {
     }                                                                                 \
   } while (0)
   H_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  H_CUDA(cudaEventCreate(&h->ev0));
-  H_CUDA(cudaEventCreate(&h->ev1));
+  for (int i = 0; i < Handle::kEvRing; i++) {
+    H_CUDA(cudaEventCreate(&h->ev_begin[i]));
+    H_CUDA(cudaEventCreate(&h->ev_end[i]));
+  }
   H_CUDA(cudaMalloc(&h->d_snp_major, (size_t)snps * h->pitch_s));
   H_CUDA(cudaMalloc(&h->d_indiv_major, (size_t)indiv * h->pitch_i));
   H_CUDA(cudaMalloc(&h->d_f, sizeof(double) * snps));
@@ -330,9 +334,24 @@ void *mb200_stream(void *compressed) {
 int mb200_dgemm_last_kernel_ms(void *compressed, float *ms) {
   Handle *h = as_handle(compressed);
   if (!h || !ms) return status().code ? status().code : -2;
+  if (h->ev_count == 0) return fail(-2, __func__, __LINE__, "no dgemm_compressed call yet");
   MB_CUDA(cudaStreamSynchronize(h->stream));
-  MB_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  const int i = (int)((h->ev_count - 1) % Handle::kEvRing);
+  MB_CUDA(cudaEventElapsedTime(ms, h->ev_begin[i], h->ev_end[i]));
   return 0;
+}
+int mb200_dgemm_kernel_times(void *compressed, int last, float *ms, int *trans) {
+  Handle *h = as_handle(compressed);
+  if (!h || !ms) return status().code ? status().code : -2;
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  if (last > Handle::kEvRing) last = Handle::kEvRing;
+  if ((unsigned long long)last > h->ev_count) last = (int)h->ev_count;
+  for (int j = 0; j < last; j++) {
+    const int i = (int)((h->ev_count - last + j) % Handle::kEvRing);
+    MB_CUDA(cudaEventElapsedTime(&ms[j], h->ev_begin[i], h->ev_end[i]));
+    if (trans) trans[j] = h->ev_trans[i];
+  }
+  return last;
 }
 int mb200_sync(void *compressed) {
   Handle *h = as_handle(compressed);

@@ -183,9 +183,12 @@ int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double
   if (o.dgemm_mode == 1 && dgemm_tc_available())
     return dgemm_tc_device(h, trans, n, dB, ldb, dC, ldc);
   MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered));
-  MB_CUDA(cudaEventRecord(h->ev0, h->stream));
+  const int ev = (int)(h->ev_count % Handle::kEvRing);
+  h->ev_trans[ev] = trans;
+  MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
   MB_CHECK(dgemm_fp64_device(h, trans, n, dB, ldb, dC, ldc));
-  MB_CUDA(cudaEventRecord(h->ev1, h->stream));
+  MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
+  h->ev_count++;
   return 0;
 }
 

@@ -1,0 +1,100 @@
+"""SNP-block sharding of dgemm_compressed over one process per GPU.
+
+The reference is single-GPU (src/cuda/dgemm_compressed_cuda.cu:43-170 uploads the whole matrix to
+one device).  Here rank g owns the SNP range S_g (boundaries multiples of 512 SNPs = one 128-byte
+line of the individual-major layout) in BOTH device orientations, so every direction streams each
+rank's shard exactly once:
+
+  'T'  C[S_g, :] = (Z[:, S_g] - 2 1 f_g^T)^T B          no communication, outputs are disjoint
+  'N'  C = sum_g (Z[:, S_g] - 2 1 f_g^T) B[S_g, :]      ONE all-reduce (sum, fp64) of indiv x n
+
+The centring term is linear in the SNP range, so each rank folds its own share into its partial
+before the reduce.  `torch.distributed` is the plumbing (NCCL on GPUs; gloo in the CPU tests,
+which inject the oracle as the local product because the library has no CPU path).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, List, Optional, Tuple
+
+BLOCK = 512  # SNPs per 128-byte line of the individual-major rows
+
+
+def partition_snps(snps: int, world: int) -> List[Tuple[int, int]]:
+    """(begin, count) per rank: contiguous, multiples of 512 SNPs except the tail, balanced to
+    within one block.  Ranks beyond the number of blocks get an empty range."""
+    if snps < 0 or world < 1:
+        raise ValueError("snps >= 0 and world >= 1 required")
+    nblocks = (snps + BLOCK - 1) // BLOCK
+    base, extra = divmod(nblocks, world)
+    out, begin = [], 0
+    for r in range(world):
+        blocks = base + (1 if r < extra else 0)
+        end = min(snps, begin + blocks * BLOCK)
+        out.append((begin, end - begin))
+        begin = end
+    assert begin == snps
+    return out
+
+
+class ShardedCompressed:
+    """Rank-local view of a SNP-block-sharded compressed matrix.
+
+    handle       C-ABI handle of THIS rank's shard (snps_local x indiv), or None when a
+                 `local_dgemm` callable is injected (tests).
+    local_dgemm  callable(trans:int, B_local, C_out) computing the rank-local centred product on
+                 tensors; defaults to mb200_dgemm_compressed_device on the handle's stream.
+    Panels: a column-major rows x n matrix is an (n, rows) row-major contiguous torch tensor.
+    """
+
+    def __init__(self, handle, snps_total: int, indiv: int, rank: int, world: int,
+                 group=None, local_dgemm: Optional[Callable] = None):
+        self.handle, self.snps_total, self.indiv = handle, snps_total, indiv
+        self.rank, self.world, self.group = rank, world, group
+        self.parts = partition_snps(snps_total, world)
+        self.s_begin, self.s_count = self.parts[rank]
+        self._local = local_dgemm or self._device_dgemm
+        self._stream = None
+
+    # -- device plumbing --------------------------------------------------------------------
+    def stream(self):
+        """The library's stream as a torch stream (so NCCL and events order against it)."""
+        import torch
+        from . import api
+        if self._stream is None:
+            ptr = api.load_library().mb200_stream(self.handle)
+            self._stream = torch.cuda.ExternalStream(ptr)
+        return self._stream
+
+    def _device_dgemm(self, trans: int, B, Cout) -> None:
+        from . import api
+        lib = api.load_library()
+        # a column-major rows x n panel is held as an (n, rows) row-major contiguous tensor
+        n = B.shape[0]
+        rc = lib.mb200_dgemm_compressed_device(trans, self.handle, n, C.c_void_p(B.data_ptr()),
+                                               B.shape[1], C.c_void_p(Cout.data_ptr()),
+                                               Cout.shape[1])
+        api._check(rc, "mb200_dgemm_compressed_device")
+
+    # -- the two directions -----------------------------------------------------------------
+    def dgemm_n(self, B_local, C_out):
+        """B_local: (n, |S_g|) this rank's rows of B; C_out: (n, indiv) -- the full product."""
+        import torch.distributed as dist
+        if self.s_count > 0:
+            self._local(0, B_local, C_out)
+        else:
+            C_out.zero_()
+        if self.world > 1:
+            if C_out.is_cuda:
+                import torch
+                with torch.cuda.stream(self.stream()):
+                    dist.all_reduce(C_out, op=dist.ReduceOp.SUM, group=self.group)
+            else:
+                dist.all_reduce(C_out, op=dist.ReduceOp.SUM, group=self.group)
+        return C_out
+
+    def dgemm_t(self, B, C_local):
+        """B: (n, indiv) replicated; C_local: (n, |S_g|) rows S_g of the result.  No exchange."""
+        if self.s_count > 0:
+            self._local(1, B, C_local)
+        return C_local
