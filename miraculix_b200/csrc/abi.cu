@@ -321,9 +321,9 @@ int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const doub
   Handle *h = as_handle(compressed);
   if (!h) return status().code;
   const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
-  if (n < 0 || ldb < k || ldc < m)
-    return fail(-2, __func__, __LINE__, "bad arguments n=%d ldb=%ld (k=%ld) ldc=%ld (m=%ld)", n, ldb,
-                k, ldc, m);
+  if (n < 0 || n > h->max_n || ldb < k || ldc < m)
+    return fail(-2, __func__, __LINE__, "bad arguments n=%d (max_n=%d) ldb=%ld (k=%ld) ldc=%ld (m=%ld)",
+                n, h->max_n, ldb, k, ldc, m);
   return dgemm_device(h, trans ? 1 : 0, n, dB, ldb, dC, ldc);
 }
 

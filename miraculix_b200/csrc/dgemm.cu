@@ -123,7 +123,8 @@ dgemm_fp64_kernel(const uint8_t *__restrict__ A, long pitch, long rows, long K,
       }
 #pragma unroll
       for (int c = 0; c < NC; c++) {
-        const double b = Bs[c * F64_BPITCH + lane * 17 + j];
+        // field j of the word is genotype 4 (j & 3) + (j >> 2) of the 16 (interleaved layout)
+        const double b = Bs[c * F64_BPITCH + lane * 17 + 4 * (j & 3) + (j >> 2)];
 #pragma unroll
         for (int r = 0; r < 4; r++) acc[r][c] = fma(d[r], b, acc[r][c]);
       }

@@ -24,7 +24,10 @@ constexpr uint32_t kHandleMagic = 0x4d423230u;  // "MB20"
 
 // HBM layout: both orientations value-coded (2-bit field = genotype 0/1/2, PLINK
 // missing -> 0), rows padded with zeros to a multiple of 128 bytes (= 512 genotypes), base
-// pointers 256-byte aligned (cudaMalloc).
+// pointers 256-byte aligned (cudaMalloc).  Inside every little-endian 32-bit word (16 genotypes
+// k = 16q .. 16q+15 of a row) the fields are interleaved: genotype 16q + 4j + b lives at bits
+// [8b + 2j, 8b + 2j + 1], so (word >> 2j) & 0x03030303 yields genotypes 16q+4j .. 16q+4j+3 as
+// four int8 -- the tensor-core kernel expands 16 genotypes with 7 integer instructions.
 struct Handle {
   uint32_t magic = kHandleMagic;
   int device = 0;

@@ -4,8 +4,9 @@
 // host-prepared orientations of the bed, and the caller-side host transposes that feed it
 // (src/bindings/Julia/compressed_operations.jl:45-66, src/bindings/Fortran/modplink_miraculix.f90:177-218).
 // Here only the SNP-major bed is read; one kernel writes both device orientations, recodes
-// PLINK codes to genotype values (MXinfo.h:143: 00->0, 01->0, 10->1, 11->2), zero-pads every
-// row to 128 bytes and accumulates the per-SNP allele counts.
+// PLINK codes to genotype values (MXinfo.h:143: 00->0, 01->0, 10->1, 11->2), interleaves the
+// fields inside every 32-bit word (see handle.h), zero-pads every row to 128 bytes and
+// accumulates the per-SNP allele counts.
 //
 // HBM-bound: algorithmic bytes = snps*ceil(indiv/4) read + snps*pitch_s + indiv*pitch_i written.
 #include "common.cuh"
@@ -17,10 +18,20 @@ constexpr int RP_TILE = 256;         // SNPs per tile = individuals per tile
 constexpr int RP_BYTES = 64;         // input bytes per SNP row of a tile (256 individuals)
 constexpr int RP_PITCH = 68;         // smem row pitch (bytes)
 
-__device__ __forceinline__ uint32_t plink_to_value_byte(uint32_t b) {
+// PLINK codes -> values on a whole 32-bit word (16 fields), MXinfo.h:143.
+__device__ __forceinline__ uint32_t plink_to_value_word(uint32_t w) {
   // per 2-bit field: value = hi + (hi & lo)  ->  value_hi = hi & lo, value_lo = hi & ~lo
-  uint32_t hi = (b >> 1) & 0x55u, lo = b & 0x55u;
+  uint32_t hi = (w >> 1) & 0x55555555u, lo = w & 0x55555555u;
   return ((hi & lo) << 1) | (hi & ~lo);
+}
+// In-word interleave of the device layout (handle.h): plain field t = 4j + b (bits 8j + 2b)
+// moves to bits 8b + 2j, i.e. a 4x4 transpose of 2-bit fields = two delta swaps.
+__device__ __forceinline__ uint32_t interleave_word(uint32_t x) {
+  uint32_t t = ((x >> 6) ^ x) & 0x00CC00CCu;
+  x ^= t ^ (t << 6);
+  t = ((x >> 12) ^ x) & 0x0000F0F0u;
+  x ^= t ^ (t << 12);
+  return x;
 }
 
 // plink: rows [s_begin, s_begin + s_count) of the bed, row pitch bs bytes, base = row s_begin.
@@ -29,44 +40,54 @@ repack_kernel(const uint8_t *__restrict__ plink, long s_begin, long s_count, lon
               long bs, uint8_t *__restrict__ snp_major, long pitch_s,
               uint8_t *__restrict__ indiv_major, long pitch_i,
               unsigned long long *__restrict__ counts) {
-  __shared__ uint8_t tile[RP_TILE * RP_PITCH];
+  __shared__ __align__(16) uint8_t tile[RP_TILE * RP_PITCH];  // value-coded, PLAIN field order
   const int tid = threadIdx.x;
   const long i0 = (long)blockIdx.x * RP_TILE;             // first individual of the tile
   const long sl0 = (long)blockIdx.y * RP_TILE;            // first SNP of the tile, chunk-local
-  const long b0 = i0 >> 2;
+  const long w0 = i0 >> 4;                                // first 32-bit word of the tile in a row
 
-  // phase 1: coalesced read of 256 rows x 64 bytes, recode, write SNP-major, stage in smem
-  for (int e = tid; e < RP_TILE * RP_BYTES; e += 256) {
-    const int r = e >> 6, cb = e & 63;
-    const long sl = sl0 + r, gb = b0 + cb;
+  // phase 1: read 256 rows x 16 words, recode, write SNP-major (interleaved), stage in smem
+  for (int e = tid; e < RP_TILE * (RP_BYTES / 4); e += 256) {
+    const int r = e >> 4, cw = e & 15;
+    const long sl = sl0 + r, gw = w0 + cw;
     uint32_t v = 0;
-    if (sl < s_count && gb < bs) {
-      v = plink_to_value_byte(plink[sl * bs + gb]);
-      const long keep = indiv - 4 * gb;                   // valid fields in this byte
-      if (keep < 4) v &= (1u << (2 * keep)) - 1u;
-      snp_major[(s_begin + sl) * pitch_s + gb] = (uint8_t)v;
+    if (sl < s_count && 4 * gw < bs) {
+      const uint8_t *src = plink + sl * bs + 4 * gw;
+      const long nbytes = bs - 4 * gw;                    // bytes of this row left (>= 1)
+      uint32_t w = src[0];
+      if (nbytes > 1) w |= (uint32_t)src[1] << 8;
+      if (nbytes > 2) w |= (uint32_t)src[2] << 16;
+      if (nbytes > 3) w |= (uint32_t)src[3] << 24;
+      v = plink_to_value_word(w);
+      const long keep = indiv - 16 * gw;                  // valid fields in this word
+      if (keep < 16) v &= (1u << (2 * keep)) - 1u;
+      *reinterpret_cast<uint32_t *>(snp_major + (s_begin + sl) * pitch_s + 4 * gw) =
+          interleave_word(v);
     }
-    tile[r * RP_PITCH + cb] = (uint8_t)v;
-    // allele count of this half row: a warp covers 32 consecutive bytes of ONE row
-    int cnt = __popc(v & 0x55u) + 2 * __popc(v & 0xAAu);
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if ((tid & 31) == 0 && cnt && sl < s_count)
+    *reinterpret_cast<uint32_t *>(tile + r * RP_PITCH + 4 * cw) = v;
+    // allele count: a half-warp covers the 16 words of ONE row
+    int cnt = __popc(v & 0x55555555u) + 2 * __popc(v & 0xAAAAAAAAu);
+    for (int o = 8; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((tid & 15) == 0 && cnt && sl < s_count)
       atomicAdd(&counts[s_begin + sl], (unsigned long long)cnt);
   }
   __syncthreads();
 
-  // phase 2: each output byte gathers one field from four consecutive SNP rows
-  const long q0 = (s_begin + sl0) >> 2;                   // s_begin, sl0 are multiples of 4
-  const long bi = (snps + 3) >> 2;
-  for (int e = tid; e < RP_TILE * RP_BYTES; e += 256) {
-    const int il = e >> 6, q = e & 63;
+  // phase 2: one interleaved output word = field `il` of 16 consecutive SNP rows
+  const long q0 = (s_begin + sl0) >> 4;                   // s_begin, sl0 are multiples of 256
+  for (int e = tid; e < RP_TILE * (RP_BYTES / 4); e += 256) {
+    const int il = e >> 4, q = e & 15;
     const long i = i0 + il, gq = q0 + q;
-    if (i < indiv && gq < bi) {
+    if (i < indiv && 16 * gq < snps) {
       const int cb = il >> 2, sh = 2 * (il & 3);
-      const uint8_t *t = tile + (4 * q) * RP_PITCH + cb;
-      uint32_t out = ((t[0] >> sh) & 3u) | (((t[RP_PITCH] >> sh) & 3u) << 2) |
-                     (((t[2 * RP_PITCH] >> sh) & 3u) << 4) | (((t[3 * RP_PITCH] >> sh) & 3u) << 6);
-      indiv_major[i * pitch_i + gq] = (uint8_t)out;
+      const uint8_t *t = tile + (16 * q) * RP_PITCH + cb;
+      uint32_t out = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+#pragma unroll
+        for (int b = 0; b < 4; b++)                       // SNP 16q + 4j + b -> bits 8b + 2j
+          out |= ((uint32_t)(t[(4 * j + b) * RP_PITCH] >> sh) & 3u) << (8 * b + 2 * j);
+      *reinterpret_cast<uint32_t *>(indiv_major + i * pitch_i + 4 * gq) = out;
     }
   }
 }

@@ -58,6 +58,16 @@ def repack(plink: np.ndarray, snps: int, indiv: int):
     return sm, im
 
 
+def unpack_device(packed: np.ndarray, cols: int) -> np.ndarray:
+    """(rows, pitch) bytes of the device layout -> (rows, cols) 2-bit values in plain order."""
+    packed = np.ascontiguousarray(packed, dtype=np.uint8)
+    rows, pitch = packed.shape
+    assert (cols + 15) // 16 * 4 <= pitch
+    out = np.zeros((rows, cols), dtype=np.uint8)
+    lib().oracle_unpack_device(_p(packed), C.c_long(rows), C.c_long(pitch), C.c_long(cols), _p(out))
+    return out
+
+
 def allele_counts(plink: np.ndarray, snps: int, indiv: int) -> np.ndarray:
     plink = np.ascontiguousarray(plink, dtype=np.uint8)
     out = np.zeros(snps, dtype=np.int64)

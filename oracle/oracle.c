@@ -71,7 +71,13 @@ EXPORT void oracle_transpose_2bit(const uint8_t *in, long rows, long cols, uint8
  *   ind_major  [indiv][pitch_i]  pitch_i = 128*ceil(ceil(snps /4)/128)
  * every 2-bit field holds the genotype VALUE 0/1/2 (PLINK2HUMAN applied, missing -> 0),
  * padding bytes and padding bit pairs are zero.  Transposition semantics as above.
+ * Within each aligned group of 16 genotypes (one little-endian 32-bit word of the row) the
+ * fields are interleaved: genotype k = 16q + 4j + b sits in byte 4q + b at bits [2j, 2j+1],
+ * so that (word >> 2j) & 0x03030303 is four consecutive genotypes as four int8.
  * ------------------------------------------------------------------------------------- */
+static inline long dev_byte(long k) { return 4 * (k / 16) + (k % 4); }
+static inline int dev_shift(long k) { return 2 * (int)((k % 16) / 4); }
+
 EXPORT void oracle_repack(const uint8_t *plink, long snps, long indiv,
                           uint8_t *snp_major, long pitch_s,
                           uint8_t *ind_major, long pitch_i) {
@@ -81,9 +87,17 @@ EXPORT void oracle_repack(const uint8_t *plink, long snps, long indiv,
   for (long s = 0; s < snps; s++)
     for (long i = 0; i < indiv; i++) {
       int v = plink2human((plink[s * bs + i / 4] >> (2 * (i % 4))) & 3);
-      snp_major[s * pitch_s + i / 4] |= (uint8_t)(v << (2 * (i % 4)));
-      ind_major[i * pitch_i + s / 4] |= (uint8_t)(v << (2 * (s % 4)));
+      snp_major[s * pitch_s + dev_byte(i)] |= (uint8_t)(v << dev_shift(i));
+      ind_major[i * pitch_i + dev_byte(s)] |= (uint8_t)(v << dev_shift(s));
     }
+}
+
+/* Inverse of the in-row interleave: packed device rows -> one value per byte, plain order. */
+EXPORT void oracle_unpack_device(const uint8_t *packed, long rows, long pitch, long cols,
+                                 uint8_t *out) {
+  for (long r = 0; r < rows; r++)
+    for (long k = 0; k < cols; k++)
+      out[r * cols + k] = (packed[r * pitch + dev_byte(k)] >> dev_shift(k)) & 3;
 }
 
 /* Allele counts per SNP: sum_i z_is (popcount rule of read_plink.jl:197-203 when there are

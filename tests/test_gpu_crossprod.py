@@ -132,7 +132,7 @@ def test_grm_properties_full_size(gpu_lib):
         _, im, cnt = api.download_layout(h)
         rng = np.random.default_rng(0)
         rows = rng.integers(0, indiv, size=24)
-        Zs = simulate.unpack_2bit(im[rows], snps).astype(np.int64)
+        Zs = cport.unpack_device(im[rows], snps).astype(np.int64)
         sub = M[torch.as_tensor(rows, device="cuda")][:, torch.as_tensor(rows, device="cuda")]
         assert np.array_equal(sub.cpu().numpy(), (Zs @ Zs.T).astype(np.float64))
         # row sums through the other kernel family (uncentred dgemm_compressed)

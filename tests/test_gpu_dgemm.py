@@ -45,7 +45,7 @@ def test_repack_bit_exact(gpu_lib, snps, indiv, missing):
         assert np.array_equal(im, im_o)
         assert np.array_equal(cnt.astype(np.int64), cport.allele_counts(plink, snps, indiv))
         # round trip against the bed itself
-        assert np.array_equal(simulate.unpack_2bit(im, snps), Z)
+        assert np.array_equal(cport.unpack_device(im, snps), Z)
         assert np.array_equal(api.get_compressed_freq(h, snps), f)
     finally:
         api.free_compressed(h)

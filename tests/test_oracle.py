@@ -72,11 +72,11 @@ def test_repack_restatement(snps, indiv):
     sm, im = cport.repack(plink, snps, indiv)
     assert sm.shape[1] % 128 == 0 and im.shape[1] % 128 == 0
     # round trip: decode(device layout) == decode(bed), element-wise
-    assert np.array_equal(simulate.unpack_2bit(im, snps), Z)
-    assert np.array_equal(simulate.unpack_2bit(sm, indiv), Z.T)
+    assert np.array_equal(cport.unpack_device(im, snps), Z)
+    assert np.array_equal(cport.unpack_device(sm, indiv), Z.T)
     # padding is zero
-    assert not simulate.unpack_2bit(im, im.shape[1] * 4)[:, snps:].any()
-    assert not simulate.unpack_2bit(sm, sm.shape[1] * 4)[:, indiv:].any()
+    assert not cport.unpack_device(im, im.shape[1] * 4)[:, snps:].any()
+    assert not cport.unpack_device(sm, sm.shape[1] * 4)[:, indiv:].any()
     # transposing twice gives the original (tests/dgemm_compressed/test.jl:79-83)
     t = cport.transpose_2bit(plink, snps, indiv)
     assert np.array_equal(cport.transpose_2bit(t, indiv, snps), plink)
