@@ -141,54 +141,60 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 16) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      int zs = 0, bs = 0;
-      uint32_t zph = 0, bph = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int rb = u % p.row_blocks, ks = u / p.row_blocks;
-        const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-        for (int kc = c0; kc < c1; kc++) {
-          mbar_wait(&b_empty[bs], bph ^ 1);
+    // ===== TMA producer (whole warp walks, one elected lane issues) =====
+    int zs = 0, bs = 0;
+    uint32_t zph = 0, bph = 0;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+      const int rb = u % p.row_blocks, ks = u / p.row_blocks;
+      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
+      for (int kc = c0; kc < c1; kc++) {
+        mbar_wait(&b_empty[bs], bph ^ 1);
+        if (elect_one()) {
           mbar_expect_tx(&b_full[bs], (uint32_t)bslot_bytes);
 #pragma unroll
           for (int sub = 0; sub < 4; sub++)
             tma_load_2d(bring + bs * bslot_bytes + sub * sub_bytes, &tmap_b, &b_full[bs],
                         kc * 512 + sub * 128, 0);
-          if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
+        }
+        __syncwarp();
+        if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
 #pragma unroll
-          for (int g = 0; g < DT_RT; g++) {
-            mbar_wait(&z_empty[zs], zph ^ 1);
+        for (int g = 0; g < DT_RT; g++) {
+          mbar_wait(&z_empty[zs], zph ^ 1);
+          if (elect_one()) {
             mbar_expect_tx(&z_full[zs], DT_ZBYTES);
             tma_load_2d(zring + zs * DT_ZBYTES, &tmap_z, &z_full[zs], kc * 128,
                         rb * (DT_RT * 128) + g * 128);
-            if (++zs == DT_ZSLOTS) { zs = 0; zph ^= 1; }
           }
+          __syncwarp();
+          if (++zs == DT_ZSLOTS) { zs = 0; zph ^= 1; }
         }
       }
     }
   } else if (warp == 17) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_i8(128, p.N, 1, 1);
-      int as = 0, bs = 0;
-      uint32_t aph = 0, bph = 0, dph = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int ks = u / p.row_blocks;
-        const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-        mbar_wait(d_empty, dph ^ 1);  // epilogue of the previous unit has drained TMEM
+    // ===== MMA issuer: the whole warp walks the protocol, one elected lane issues (a lane==0
+    // branch makes ptxas wrap every UTCIMMA in a uniformisation loop: 60 instead of 45 cycles
+    // per MMA, scripts/probes/mma_probe.cu) =====
+    const uint32_t idesc = make_idesc_i8(128, p.N, 1, 1);
+    int as = 0, bs = 0;
+    uint32_t aph = 0, bph = 0, dph = 0;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+      const int ks = u / p.row_blocks;
+      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
+      mbar_wait(d_empty, dph ^ 1);  // epilogue of the previous unit has drained TMEM
+      tc_fence_after();
+      for (int kc = c0; kc < c1; kc++) {
+        mbar_wait(&b_full[bs], bph);
         tc_fence_after();
-        for (int kc = c0; kc < c1; kc++) {
-          mbar_wait(&b_full[bs], bph);
-          tc_fence_after();
-          const uint32_t bbase = smem_u32(bring + bs * bslot_bytes);
+        const uint32_t bbase = smem_u32(bring + bs * bslot_bytes);
 #pragma unroll
-          for (int sub = 0; sub < 4; sub++) {
-            const uint64_t bdesc = make_desc_k_sw128(bbase + sub * sub_bytes);
+        for (int sub = 0; sub < 4; sub++) {
+          const uint64_t bdesc = make_desc_k_sw128(bbase + sub * sub_bytes);
 #pragma unroll
-            for (int g = 0; g < DT_RT; g++) {
-              mbar_wait(&a_full[as], aph);
-              tc_fence_after();
+          for (int g = 0; g < DT_RT; g++) {
+            mbar_wait(&a_full[as], aph);
+            tc_fence_after();
+            if (elect_one()) {
               const uint32_t d_tmem = tmem_base + g * p.N;
               const uint32_t a_tmem = tmem_base + DT_ACOL0 + as * 32;
 #pragma unroll
@@ -196,15 +202,18 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
                 mma_i8_ts(d_tmem, a_tmem + 8 * k4, bdesc + 2 * k4, idesc,
                           (kc > c0 || sub > 0 || k4 > 0) ? 1u : 0u);
               tc_commit(&a_empty[as]);
-              if (++as == DT_ASLOTS) { as = 0; aph ^= 1; }
             }
+            __syncwarp();
+            if (++as == DT_ASLOTS) { as = 0; aph ^= 1; }
           }
-          tc_commit(&b_empty[bs]);
-          if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
         }
-        tc_commit(d_full);
-        dph ^= 1;
+        if (elect_one()) tc_commit(&b_empty[bs]);
+        __syncwarp();
+        if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
       }
+      if (elect_one()) tc_commit(d_full);
+      __syncwarp();
+      dph ^= 1;
     }
   } else {
     // ===== expanders (and epilogue): group g owns row tile g, thread = row = TMEM lane =====
