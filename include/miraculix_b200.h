@@ -99,6 +99,9 @@ int mb200_dgemm_last_kernel_ms(void *compressed, float *ms);
  * Synchronises the stream.  Returns the number of entries written, or a negative status. */
 int mb200_dgemm_kernel_times(void *compressed, int last, float *ms, int *trans);
 int mb200_sync(void *compressed);
+/* Developer aid: with MB200_TRACE=1 the tensor-core dgemm kernel accumulates clock64() segments
+ * of one expander warp ([0..7]) and of the MMA warp ([16..19]) of CTA 0; this reads them. */
+int mb200_debug_read_trace(long long *out, int n);
 
 /* Build a handle from a bed payload that already lives on the device (same layout as the
  * host one).  d_f may be NULL: then f is computed on the device from the allele counts. */

@@ -107,6 +107,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   }
 }
 
+// Warp-uniform wait: every lane polls, the vote makes the loop branch provably uniform, so ptxas
+// keeps the ring counters and descriptors that follow in uniform registers (no R2UR chains in
+// front of every UTCIMMA / UTMALDG).  All 32 lanes must call it.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+    if (++spins >= 4096u) {
+      if (t0 == 0) t0 = global_timer_ns();
+      else if (global_timer_ns() - t0 > 4000000000ull) __trap();
+    }
+  }
+}
+
 // 2-D TMA tile load, completes on an mbarrier.  c0 = innermost coordinate.
 __device__ __forceinline__ void tma_load_2d(void *dst, const void *tmap, uint64_t *bar, int c0,
                                             int c1) {

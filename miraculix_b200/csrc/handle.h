@@ -69,6 +69,8 @@ int freq_from_counts(Handle *h);  // d_f = counts / (2 indiv)
 // dgemm.cu
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
 
+int dgemm_tc_read_trace(long long *out, int n);  // dgemm_tc.cu, MB200_TRACE=1
+
 // crossprod.cu
 struct CrossprodTiming {
   double gemm_ms = 0, epilogue_ms = 0, executed_ops = 0;
