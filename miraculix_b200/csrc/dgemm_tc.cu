@@ -13,12 +13,12 @@
 // micro-kernel dgemm_compressed_cuda.h:253-268).  Kernels:
 //   colmax_kernel     amax_c = max_k |B[k,c]|
 //   quantize_kernel   Bq[(c*S + j)][k] = digit j of rint(B[k,c] * 2^(P - e_c))       (int8, K-major)
-//   dgemm_tc_kernel   persistent, warp-specialised, one CTA per SM:
-//       warps 16,18  TMA producers: packed Z tiles [128 rows x 128 B] (swizzle 128B); Bq tiles
-//       warps 0..15  expanders: 2-bit -> int8 (7 integer ops per 16 genotypes thanks to the
-//                    interleaved layout), tcgen05.st into the TMEM A-operand ring; epilogue
-//       warp 17      MMA issuer: tcgen05.mma kind::i8, M=128, N=16..80, K=32, A from TMEM,
-//                    B (digits) from shared memory, int32 accumulators in TMEM
+//   dgemm_tc_kernel   persistent, warp-specialised, one CTA per SM (see "main kernel" below):
+//       expanders: TMA-fed packed Z tiles [128 rows x 128 B] (swizzle 128B) -> 2-bit -> int8
+//                  (7 integer ops per 16 genotypes thanks to the interleaved layout) ->
+//                  tcgen05.st into the TMEM A-operand slots; epilogue
+//       MMA issuers: tcgen05.mma kind::i8, M=128, N=16..80, K=32, A from TMEM, B (digits) from
+//                  shared memory, int32 accumulators in TMEM
 //   HBM-bound by design: algorithmic bytes = the packed matrix once (+ B, C).
 #include <cuda.h>
 #include <math.h>
@@ -79,46 +79,85 @@ quantize_kernel(const double *__restrict__ B, long ldb, long k, int ncols, int S
 
 // ---------------------------------------------------------------------------------------------
 // main kernel
+//
+// A CTA owns R row tiles of 128 rows ("groups") and walks K in chunks of 512 genotypes.  Each
+// group is an independent pipeline with its own packed-Z slots, TMEM A-operand ring, TMEM
+// accumulator, four expander warps and its own MMA-issuing warp; the groups only share the digit
+// tiles Bq in shared memory.  One issuing warp per group matters: the bookkeeping around a slot
+// (mbarrier try_wait ~90 cycles even when complete, elect, commit; scripts/probes/instr_probe.cu)
+// costs ~300 cycles of one warp's serial time against ~160 cycles of tensor work per slot, so a
+// single issuer for all groups caps the kernel at half the tensor rate.
+//
+//   warps 0..15   expanders, group g = warp / 4, TMEM lane quarter w = warp % 4 (thread = row)
+//   warps 16..19  MMA issuer of group warp - 16
+//   warp  20      TMA producer of the digit tiles
 // ---------------------------------------------------------------------------------------------
-constexpr int DT_RT = 4;                   // row tiles (of 128 rows) per CTA = TMEM accumulators
+constexpr int DT_RMAX = 4;                 // groups (row tiles of 128 rows) per CTA
 constexpr int DT_NMAX = 80;                // max MMA N (digit rows) per pass
-constexpr int DT_ZSLOTS = 8;               // packed-Z ring: [128 rows][128 B] = 16 KB each
+constexpr int DT_ZSLOTS = 2;               // packed-Z slots per group: [128 rows][128 B] = 16 KB
 constexpr int DT_ZBYTES = 128 * 128;
 constexpr int DT_BSLOTS = 4;               // digit ring: 2 sub-tiles [N rows][128 B] per slot (K = 256)
-constexpr int DT_ASLOTS = 6;               // TMEM A-operand ring: 32 columns (K = 128) each
-constexpr int DT_ACOL0 = DT_RT * DT_NMAX;  // 320: accumulators below, A ring above
-constexpr int DT_THREADS = 19 * 32;
-constexpr int DT_NBAR = 2 * DT_ZSLOTS + 2 * DT_BSLOTS + 2 * DT_ASLOTS + 2;
+constexpr int DT_ASLOTS = 2;               // TMEM A-operand slots per group: 32 columns (K = 128) each
+constexpr int DT_THREADS = 21 * 32;
+constexpr int DT_NBAR = DT_RMAX * (DT_ZSLOTS + 2 * DT_ASLOTS + 2) + 2 * DT_BSLOTS;
 
 __host__ __device__ constexpr int dt_smem_bytes(int N) {
-  return DT_ZSLOTS * DT_ZBYTES + DT_BSLOTS * 2 * N * 128 + 1024 /*align*/ + 8 * DT_NBAR + 16;
+  return DT_RMAX * DT_ZSLOTS * DT_ZBYTES + DT_BSLOTS * 2 * N * 128 + 1024 /*align*/ +
+         8 * DT_NBAR + 16;
 }
+// groups that fit TMEM: R * N accumulator columns + R * 2 * 32 A-ring columns <= 512
+__host__ __device__ constexpr int dt_groups(int N) { return N <= 64 ? 4 : 3; }
 
 struct DtParams {
   long rows;            // rows of the packed matrix used (indiv for 'N', snps for 'T')
   int nchunks;          // K chunks of 512 genotypes (= 128 packed bytes per row)
-  int row_blocks;       // ceil(rows / 512)
+  int R;                // groups per CTA (3 or 4)
+  int row_blocks;       // ceil(rows / (128 R))
   int ksplits, cps;     // K splits and chunks per split
   int N, S, ncols;      // MMA N (multiple of 16), digits per column, columns this pass
   double *C;            // centre-initialised output, column-major
   long ldc;
   const int *exps;      // e_c per column
-  int dbg;              // TRACE builds only: 1 skip tcgen05.st, 2 skip MMAs, 4 skip LDS of Z, 8 skip ALU
+  int dbg;              // TRACE builds only: 1 skip tcgen05.st, 2 skip MMAs
+  int flags;            // MB200_TC_FLAGS: 1 = no look-ahead barrier polls in the MMA warps
 };
 
 // Optional cycle accounting (MB200_TRACE=1): CTA 0 accumulates clock64() segments of expander
-// warp 0 and of the MMA warp into g_dt_trace; read back with mb200_debug_read_trace.
+// warp 0 ([0..7]) and of MMA warp 16 ([16..23]); read back with mb200_debug_read_trace.
 __device__ long long g_dt_trace[32];
-// timeline of ring slots [DT_EV0, DT_EV0 + 256) of CTA 0: [0] expander passes a_empty, [1] expander
-// arrives a_full, [2] MMA warp passes a_full, [3] MMA warp done issuing, [4] z_full passed (per chunk)
-constexpr unsigned DT_EV0 = 4096;
-__device__ long long g_dt_events[5][256];
 #define DT_SEG(slot)                                   \
   if (TRACE) {                                         \
     const long long _now = clock64();                  \
     tr[slot] += _now - tlast;                          \
     tlast = _now;                                      \
   }
+
+// The CTA's work list as a stream of K chunks: unit u = blockIdx.x + i gridDim.x covers chunks
+// [c0, c1) of row block rb.  Every role walks the same stream with its own cursor.
+struct DtCursor {
+  int u, rb, kc, c1;
+  bool first;  // kc is the first chunk of its unit
+  __device__ __forceinline__ void open(const DtParams &p, int unit) {
+    u = unit;
+    rb = u % p.row_blocks;
+    const int ks = u / p.row_blocks;
+    kc = ks * p.cps;
+    c1 = min(kc + p.cps, p.nchunks);
+    first = true;
+  }
+  __device__ __forceinline__ bool valid(const DtParams &p) const {
+    return u < p.row_blocks * p.ksplits;
+  }
+  __device__ __forceinline__ bool last() const { return kc + 1 == c1; }
+  __device__ __forceinline__ void next(const DtParams &p, int stride) {
+    if (++kc == c1) open(p, u + stride);
+    else first = false;
+  }
+};
+
+__device__ __forceinline__ void group_bar_sync(int g) {  // named barrier 1 + g, 128 threads
+  asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+}
 
 template <bool TRACE>
 __global__ void __launch_bounds__(DT_THREADS, 1)
@@ -127,91 +166,77 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
-  uint8_t *zring = smem;
-  uint8_t *bring = smem + DT_ZSLOTS * DT_ZBYTES;
+  uint8_t *zring = smem;                                         // [group][slot][128][128 B]
+  uint8_t *bring = smem + DT_RMAX * DT_ZSLOTS * DT_ZBYTES;
   const int sub_bytes = p.N * 128;          // one digit sub-tile: N rows x 128 K-bytes
   const int bslot_bytes = 2 * sub_bytes;    // half a K chunk: 256
   uint64_t *bars = reinterpret_cast<uint64_t *>(bring + DT_BSLOTS * bslot_bytes);
-  uint64_t *z_full = bars, *z_empty = z_full + DT_ZSLOTS;
-  uint64_t *b_full = z_empty + DT_ZSLOTS, *b_empty = b_full + DT_BSLOTS;
-  uint64_t *a_full = b_empty + DT_BSLOTS, *a_empty = a_full + DT_ASLOTS;
-  uint64_t *d_full = a_empty + DT_ASLOTS, *d_empty = d_full + 1;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(d_empty + 1);
+  uint64_t *z_full = bars;                                   // [g][DT_ZSLOTS]
+  uint64_t *a_full = z_full + DT_RMAX * DT_ZSLOTS;           // [g][DT_ASLOTS]
+  uint64_t *a_empty = a_full + DT_RMAX * DT_ASLOTS;          // [g][DT_ASLOTS]
+  uint64_t *d_full = a_empty + DT_RMAX * DT_ASLOTS;          // [g]
+  uint64_t *d_empty = d_full + DT_RMAX;                      // [g]
+  uint64_t *b_full = d_empty + DT_RMAX, *b_empty = b_full + DT_BSLOTS;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(b_empty + DT_BSLOTS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_units = p.row_blocks * p.ksplits;
+  const int R = p.R;
+  const int stride = gridDim.x;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < DT_ZSLOTS; i++) { mbar_init(&z_full[i], 1); mbar_init(&z_empty[i], 4); }
-    for (int i = 0; i < DT_BSLOTS; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < DT_ASLOTS; i++) { mbar_init(&a_full[i], 4); mbar_init(&a_empty[i], 1); }
-    mbar_init(d_full, 1);
-    mbar_init(d_empty, 16);
+    for (int i = 0; i < DT_RMAX * DT_ZSLOTS; i++) mbar_init(&z_full[i], 1);
+    for (int i = 0; i < DT_RMAX * DT_ASLOTS; i++) { mbar_init(&a_full[i], 4); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < DT_RMAX; i++) { mbar_init(&d_full[i], 1); mbar_init(&d_empty[i], 4); }
+    for (int i = 0; i < DT_BSLOTS; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], R); }
     fence_mbar_init();
     tma_prefetch_desc(&tmap_z);
     tma_prefetch_desc(&tmap_b);
   }
-  if (warp == 17) tmem_alloc(tmem_slot, 512);
+  if (warp == 20) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t acol0 = (uint32_t)(R * p.N);  // accumulators below, A slots above
 
-  if (warp == 16) {
-    // ===== TMA producer of the packed matrix (whole warp walks, one elected lane issues) =====
-    int zs = 0;
-    uint32_t zph = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const int rb = u % p.row_blocks, ks = u / p.row_blocks;
-      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-      for (int kc = c0; kc < c1; kc++) {
-#pragma unroll
-        for (int g = 0; g < DT_RT; g++) {
-          mbar_wait_warp(&z_empty[zs], zph ^ 1);
-          if (elect_one()) {
-            mbar_expect_tx(&z_full[zs], DT_ZBYTES);
-            tma_load_2d(zring + zs * DT_ZBYTES, &tmap_z, &z_full[zs], kc * 128,
-                        rb * (DT_RT * 128) + g * 128);
-          }
-          __syncwarp();
-          if (++zs == DT_ZSLOTS) { zs = 0; zph ^= 1; }
-        }
-      }
-    }
-  } else if (warp == 18) {
-    // ===== TMA producer of the digit panel (its own warp: the two rings never block each other)
+  if (warp == 20) {
+    // ===== TMA producer of the digit tiles (whole warp walks, one elected lane issues) =====
     int bs = 0;
     uint32_t bph = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const int ks = u / p.row_blocks;
-      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-      for (int kh = 2 * c0; kh < 2 * c1; kh++) {  // half chunks of K = 256
+    DtCursor c;
+    for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride)) {
+#pragma unroll
+      for (int half = 0; half < 2; half++) {
         mbar_wait_warp(&b_empty[bs], bph ^ 1);
         if (elect_one()) {
+          const int k0 = c.kc * 512 + half * 256;
           mbar_expect_tx(&b_full[bs], (uint32_t)bslot_bytes);
-          tma_load_2d(bring + bs * bslot_bytes, &tmap_b, &b_full[bs], kh * 256, 0);
-          tma_load_2d(bring + bs * bslot_bytes + sub_bytes, &tmap_b, &b_full[bs], kh * 256 + 128, 0);
+          tma_load_2d(bring + bs * bslot_bytes, &tmap_b, &b_full[bs], k0, 0);
+          tma_load_2d(bring + bs * bslot_bytes + sub_bytes, &tmap_b, &b_full[bs], k0 + 128, 0);
         }
         __syncwarp();
         if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
       }
     }
-  } else if (warp == 17) {
-    // ===== MMA issuer: the whole warp walks the protocol, one elected lane issues (a lane==0
-    // branch makes ptxas wrap every UTCIMMA in a uniformisation loop: 60 instead of 45 cycles
-    // per MMA, scripts/probes/mma_probe.cu) =====
-    const uint32_t idesc = make_idesc_i8(128, p.N, 1, 1);
-    int as = 0, bs = 0;
-    uint32_t aph = 0, bph = 0, dph = 0;
-    long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = TRACE ? clock64() : 0;
-    bool a_ready = false, b_ready = false;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const int ks = u / p.row_blocks;
-      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-      mbar_wait_warp(d_empty, dph ^ 1);  // epilogue of the previous unit has drained TMEM
-      tc_fence_after();
-      DT_SEG(0)
-      for (int kc = c0; kc < c1; kc++) {
+  } else if (warp >= 16) {
+    // ===== MMA issuer of group g: the whole warp walks the protocol, one elected lane issues
+    // (a lane==0 branch makes ptxas wrap every UTCIMMA in a uniformisation loop) =====
+    const int g = warp - 16;
+    if (g < R) {
+      const uint32_t idesc = make_idesc_i8(128, p.N, 0, 1);  // A u8 (0/64/128), B s8 digits
+      const uint32_t d_tmem = tmem_base + g * p.N;
+      uint64_t *af = a_full + g * DT_ASLOTS, *ae = a_empty + g * DT_ASLOTS;
+      int as = 0, bs = 0;
+      uint32_t aph = 0, bph = 0, dph = 0;
+      bool a_ready = false, b_ready = false;
+      long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = TRACE ? clock64() : 0;
+      DtCursor c;
+      for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride)) {
+        if (c.first) {
+          mbar_wait_warp(&d_empty[g], dph ^ 1);  // epilogue of the previous unit drained D
+          tc_fence_after();
+          DT_SEG(0)
+        }
 #pragma unroll
         for (int sub = 0; sub < 4; sub++) {
           if ((sub & 1) == 0) {
@@ -221,148 +246,163 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
           }
           const uint64_t bdesc =
               make_desc_k_sw128(smem_u32(bring + bs * bslot_bytes) + (sub & 1) * sub_bytes);
+          if (!a_ready) mbar_wait_warp(&af[as], aph);
+          tc_fence_after();
+          DT_SEG(2)
+          // a try_wait costs ~90 cycles even on a completed barrier: poll the NEXT slots now and
+          // consume the answers after this slot's MMAs are issued
+          const int as_n = as ^ 1;
+          const uint32_t aph_n = as ? aph ^ 1 : aph;
+          const bool a_poll = (p.flags & 1) ? false : mbar_try_wait(&af[as_n], aph_n);
+          const int bs_n = bs + 1 == DT_BSLOTS ? 0 : bs + 1;
+          const uint32_t bph_n = bs + 1 == DT_BSLOTS ? bph ^ 1 : bph;
+          bool b_poll = false;
+          if ((sub & 1) && !(p.flags & 1)) b_poll = mbar_try_wait(&b_full[bs_n], bph_n);
+          if (elect_one()) {
+            const uint32_t a_tmem = tmem_base + acol0 + (g * DT_ASLOTS + as) * 32;
 #pragma unroll
-          for (int g = 0; g < DT_RT; g++) {
-            if (!a_ready) mbar_wait_warp(&a_full[as], aph);
-            tc_fence_after();
-            DT_SEG(2)
-            // A try_wait costs ~90 cycles even on a completed barrier (scripts/probes/
-            // instr_probe.cu): poll the NEXT ring slots now, consume the answer after the MMAs
-            // of this slot have been issued, so the latency hides behind their execution.
-            const int as_n = as + 1 == DT_ASLOTS ? 0 : as + 1;
-            const uint32_t aph_n = as + 1 == DT_ASLOTS ? aph ^ 1 : aph;
-            const bool a_poll = mbar_try_wait(&a_full[as_n], aph_n);
-            const bool last_of_b = (sub & 1) && g == DT_RT - 1;
-            const int bs_n = bs + 1 == DT_BSLOTS ? 0 : bs + 1;
-            const uint32_t bph_n = bs + 1 == DT_BSLOTS ? bph ^ 1 : bph;
-            bool b_poll = false;
-            if (last_of_b) b_poll = mbar_try_wait(&b_full[bs_n], bph_n);
-            DT_SEG(4)
-            if (elect_one()) {
-              const uint32_t d_tmem = tmem_base + g * p.N;
-              const uint32_t a_tmem = tmem_base + DT_ACOL0 + as * 32;
-#pragma unroll
-              for (int k4 = 0; k4 < 4; k4++)  // K = 32 per MMA: 8 TMEM columns of A, 32 B of Bq
-                if (!TRACE || !(p.dbg & 2))
+            for (int k4 = 0; k4 < 4; k4++)  // K = 32 per MMA: 8 TMEM columns of A, 32 B of Bq
+              if (!TRACE || !(p.dbg & 2))
                 mma_i8_ts(d_tmem, a_tmem + 8 * k4, bdesc + 2 * k4, idesc,
-                          (kc > c0 || sub > 0 || k4 > 0) ? 1u : 0u);
-              DT_SEG(5)
-              tc_commit(&a_empty[as]);
-              if (last_of_b) tc_commit(&b_empty[bs]);
-              DT_SEG(6)
-            }
-            __syncwarp();
-            DT_SEG(7)
-            a_ready = __all_sync(0xffffffffu, a_poll);
-            if (last_of_b) b_ready = __all_sync(0xffffffffu, b_poll);
-            DT_SEG(3)
-            as = as_n;
-            aph = aph_n;
+                          (!c.first || sub > 0 || k4 > 0) ? 1u : 0u);
+            tc_commit(&ae[as]);
+            if (sub & 1) tc_commit(&b_empty[bs]);
+            if (sub == 3 && c.last()) tc_commit(&d_full[g]);
           }
+          __syncwarp();
+          a_ready = __all_sync(0xffffffffu, a_poll);
           if (sub & 1) {
-            bs = bs + 1 == DT_BSLOTS ? 0 : bs + 1;
-            if (bs == 0) bph ^= 1;
+            b_ready = __all_sync(0xffffffffu, b_poll);
+            bs = bs_n;
+            bph = bph_n;
           }
+          as = as_n;
+          aph = aph_n;
+          DT_SEG(3)
         }
+        if (c.last()) dph ^= 1;
       }
-      if (elect_one()) tc_commit(d_full);
-      __syncwarp();
-      dph ^= 1;
+      if (TRACE && blockIdx.x == 0 && g == 0 && lane == 0)
+        for (int i = 0; i < 8; i++) g_dt_trace[16 + i] = tr[i];
     }
-    if (TRACE && blockIdx.x == 0 && lane == 0)
-      for (int i = 0; i < 8; i++) g_dt_trace[16 + i] = tr[i];
   } else {
     // ===== expanders (and epilogue): group g owns row tile g, thread = row = TMEM lane =====
     const int g = warp >> 2, w = warp & 3;
-    const int r = 32 * w + lane;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(32 * w) << 16);
-    const int P = 8 * p.S - 2;
-    uint32_t cnt = 0;  // K chunks processed by this CTA so far
-    uint32_t dph = 0;
-    long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = TRACE ? clock64() : 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const int rb = u % p.row_blocks, ks = u / p.row_blocks;
-      const int c0 = ks * p.cps, c1 = min(c0 + p.cps, p.nchunks);
-      for (int kc = c0; kc < c1; kc++, cnt++) {
-        const uint32_t zseq = cnt * DT_RT + g;
-        const int zs = zseq % DT_ZSLOTS;
-        mbar_wait(&z_full[zs], (zseq / DT_ZSLOTS) & 1);
+    if (g < R) {
+      const int r = 32 * w + lane;
+      const uint32_t lane_base = tmem_base + ((uint32_t)(32 * w) << 16);
+      const uint32_t a_col = acol0 + g * DT_ASLOTS * 32;
+      const int P = 8 * p.S - 2 + 6;  // + 6: the A operand carries 64 x genotype
+      uint8_t *zslots = zring + g * DT_ZSLOTS * DT_ZBYTES;
+      uint64_t *zf = z_full + g * DT_ZSLOTS;
+      uint64_t *af = a_full + g * DT_ASLOTS, *ae = a_empty + g * DT_ASLOTS;
+      uint32_t q = 0;    // K chunks processed by this group so far
+      uint32_t dph = 0;
+      long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = TRACE ? clock64() : 0;
+
+      // warp 0 of the group is also the TMA producer of the group's packed-Z slots: it keeps a
+      // second cursor DT_ZSLOTS chunks ahead and refills a slot as soon as all four warps have
+      // read it (named barrier), so no separate producer warp or empty-barrier is needed.
+      DtCursor pc;
+      pc.open(p, blockIdx.x);
+      if (w == 0) {
+#pragma unroll
+        for (int s = 0; s < DT_ZSLOTS; s++) {
+          if (pc.valid(p)) {
+            if (elect_one()) {
+              mbar_expect_tx(&zf[s], DT_ZBYTES);
+              tma_load_2d(zslots + s * DT_ZBYTES, &tmap_z, &zf[s], pc.kc * 128,
+                          (pc.rb * R + g) * 128);
+            }
+            __syncwarp();
+            pc.next(p, stride);
+          }
+        }
+      }
+
+      DtCursor c;
+      for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride), q++) {
+        const int zs = q & (DT_ZSLOTS - 1);
+        mbar_wait(&zf[zs], (q / DT_ZSLOTS) & 1);
         DT_SEG(0)
-        if (TRACE && blockIdx.x == 0 && w == 0 && lane == 0 && cnt * 16 + g - DT_EV0 < 256u)
-          g_dt_events[4][cnt * 16 + g - DT_EV0] = clock64();
-        const uint8_t *zrow = zring + zs * DT_ZBYTES + r * 128;
+        const uint8_t *zrow = zslots + zs * DT_ZBYTES + r * 128;
         uint4 v[8];
 #pragma unroll
-        for (int c = 0; c < 8; c++)  // 128-byte swizzle: 16-byte chunk index ^ (row & 7)
-          if (!TRACE || !(p.dbg & 4))
-            v[c] = *reinterpret_cast<const uint4 *>(zrow + ((c ^ (r & 7)) << 4));
-          else
-            v[c] = make_uint4(cnt, r, c, kc);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&z_empty[zs]);
+        for (int cc = 0; cc < 8; cc++)  // 128-byte swizzle: 16-byte chunk index ^ (row & 7)
+          v[cc] = *reinterpret_cast<const uint4 *>(zrow + ((cc ^ (r & 7)) << 4));
+        group_bar_sync(g);  // all 128 rows of the slot are in registers
+        if (w == 0) {
+          if (pc.valid(p)) {
+            if (elect_one()) {
+              mbar_expect_tx(&zf[zs], DT_ZBYTES);
+              tma_load_2d(zslots + zs * DT_ZBYTES, &tmap_z, &zf[zs], pc.kc * 128,
+                          (pc.rb * R + g) * 128);
+            }
+            __syncwarp();
+            pc.next(p, stride);
+          }
+        }
         DT_SEG(1)
 #pragma unroll
         for (int sub = 0; sub < 4; sub++) {
-          const uint32_t t = (cnt * 4 + sub) * DT_RT + g;
-          const int as = t % DT_ASLOTS;
-          mbar_wait(&a_empty[as], ((t / DT_ASLOTS) & 1) ^ 1);
+          const uint32_t t = q * 4 + sub;
+          const int as = t & 1;
+          mbar_wait(&ae[as], ((t >> 1) & 1) ^ 1);
           tc_fence_after();
           DT_SEG(2)
-          if (TRACE && blockIdx.x == 0 && w == 0 && lane == 0 && t - DT_EV0 < 256u)
-            g_dt_events[0][t - DT_EV0] = clock64();
           const uint32_t wds[8] = {v[2 * sub].x, v[2 * sub].y, v[2 * sub].z, v[2 * sub].w,
                                    v[2 * sub + 1].x, v[2 * sub + 1].y, v[2 * sub + 1].z,
                                    v[2 * sub + 1].w};
           uint32_t a[32];
 #pragma unroll
-          for (int q = 0; q < 8; q++)
+          for (int qq = 0; qq < 8; qq++)
 #pragma unroll
-            for (int j = 0; j < 4; j++)
-              a[4 * q + j] = (TRACE && (p.dbg & 8)) ? wds[q] : (wds[q] >> (2 * j)) & 0x03030303u;
-          if (!TRACE || !(p.dbg & 1))
-          tmem_st_32x32b_x32(lane_base + DT_ACOL0 + as * 32, a);
+            for (int j = 0; j < 4; j++)  // genotype value x 64 as u8: LEFT shifts run on the FMA
+              a[4 * qq + j] = (wds[qq] << (2 * (3 - j))) & 0xC0C0C0C0u;  // pipe (IMAD.SHL)
+          if (!TRACE || !(p.dbg & 1)) tmem_st_32x32b_x32(lane_base + a_col + as * 32, a);
           DT_SEG(3)
           tmem_st_wait();
           DT_SEG(4)
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&a_full[as]);
-          if (TRACE && blockIdx.x == 0 && w == 0 && lane == 0 && t - DT_EV0 < 256u)
-            g_dt_events[1][t - DT_EV0] = clock64();
+          if (lane == 0) mbar_arrive(&af[as]);
           DT_SEG(5)
         }
-      }
-      // ---- epilogue of the unit: exact recombination of the digit sums, fp64 atomics into C
-      mbar_wait(d_full, dph);
-      dph ^= 1;
-      tc_fence_after();
-      DT_SEG(6)
-      const long row = (long)rb * (DT_RT * 128) + g * 128 + r;
-      for (int c = 0; c < p.ncols; c++) {
-        uint32_t d[8];
-        tmem_ld_32x32b_x8(lane_base + g * p.N + c * p.S, d);
-        tmem_ld_wait();
-        long long lo = 0, hi = 0;  // sum_j 256^j d_j = hi 2^32 + lo, exact in 64-bit integers
+        if (c.last()) {
+          // ---- epilogue of the unit: exact recombination of the digit sums, fp64 atomics into C
+          mbar_wait(&d_full[g], dph);
+          dph ^= 1;
+          tc_fence_after();
+          DT_SEG(6)
+          const long row = ((long)c.rb * R + g) * 128 + r;
+          for (int col = 0; col < p.ncols; col++) {
+            uint32_t d[8];
+            tmem_ld_32x32b_x8(lane_base + g * p.N + col * p.S, d);
+            tmem_ld_wait();
+            long long lo = 0, hi = 0;  // sum_j 256^j d_j = hi 2^32 + lo, exact in 64-bit integers
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-          if (j < p.S) lo += (long long)(int)d[j] << (8 * j);
+            for (int j = 0; j < 4; j++)
+              if (j < p.S) lo += (long long)(int)d[j] << (8 * j);
 #pragma unroll
-        for (int j = 4; j < 8; j++)
-          if (j < p.S) hi += (long long)(int)d[j] << (8 * (j - 4));
-        const double val = fma((double)hi, 4294967296.0, (double)lo);
-        if (row < p.rows) atomicAdd(&p.C[row + (size_t)c * p.ldc], scalbn(val, p.exps[c] - P));
+            for (int j = 4; j < 8; j++)
+              if (j < p.S) hi += (long long)(int)d[j] << (8 * (j - 4));
+            const double val = fma((double)hi, 4294967296.0, (double)lo);
+            if (row < p.rows)
+              atomicAdd(&p.C[row + (size_t)col * p.ldc], scalbn(val, p.exps[col] - P));
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&d_empty[g]);
+          DT_SEG(7)
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(d_empty);
-      DT_SEG(7)
+      if (TRACE && blockIdx.x == 0 && threadIdx.x == 0)
+        for (int i = 0; i < 8; i++) g_dt_trace[i] = tr[i];
     }
-    if (TRACE && blockIdx.x == 0 && threadIdx.x == 0)
-      for (int i = 0; i < 8; i++) g_dt_trace[i] = tr[i];
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 17) {
+  if (warp == 20) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
@@ -436,11 +476,13 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
     DtParams p;
     p.rows = rows;
     p.nchunks = (int)(pitch / 128);
-    p.row_blocks = (int)ceil_div(rows, DT_RT * 128);
+    p.R = dt_groups(N);
+    p.row_blocks = (int)ceil_div(rows, p.R * 128);
     long ksplits = ceil_div(20L * h->sm_count, p.row_blocks);
     if (ksplits > p.nchunks / 8) ksplits = p.nchunks / 8;
     if (ksplits < 1) ksplits = 1;
-    p.cps = (int)ceil_div(p.nchunks, ksplits);
+    if (ksplits < ceil_div(p.nchunks, 128)) ksplits = ceil_div(p.nchunks, 128);  // int32 headroom:
+    p.cps = (int)ceil_div(p.nchunks, ksplits);  // 65536 K x (128 x 128) per term < 2^31
     p.ksplits = (int)ceil_div(p.nchunks, p.cps);
     p.N = N;
     p.S = S;
@@ -449,6 +491,7 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
     p.ldc = ldc;
     p.exps = d_exps;
     p.dbg = 0;
+    { static int fl = -1; if (fl < 0) { const char *e = getenv("MB200_TC_FLAGS"); fl = e ? atoi(e) : 0; } p.flags = fl; }
     if (trace) { const char *e = getenv("MB200_DBG"); p.dbg = e ? atoi(e) : 0; }
     const long units = (long)p.row_blocks * p.ksplits;
     const int grid = (int)(units < h->sm_count ? units : h->sm_count);
@@ -465,13 +508,8 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
 }
 
 int dgemm_tc_read_trace(long long *out, int n) {
-  if (n <= 32) {
-    MB_CUDA(cudaMemcpyFromSymbol(out, g_dt_trace, sizeof(long long) * n));
-  } else {  // 32 counters followed by the 5 x 256 event timeline
-    MB_CUDA(cudaMemcpyFromSymbol(out, g_dt_trace, sizeof(long long) * 32));
-    const int m = n - 32 < 5 * 256 ? n - 32 : 5 * 256;
-    MB_CUDA(cudaMemcpyFromSymbol(out + 32, g_dt_events, sizeof(long long) * m));
-  }
+  if (n > 32) n = 32;
+  MB_CUDA(cudaMemcpyFromSymbol(out, g_dt_trace, sizeof(long long) * n));
   return 0;
 }
 

@@ -25,31 +25,23 @@ B = torch.randn((ncol, snps), dtype=torch.float64, device=dev)
 Cn = torch.empty((ncol, indiv), dtype=torch.float64, device=dev)
 names = ["z_full wait", "LDS + z_empty arrive", "a_empty wait", "expand ALU + st issue", "wait::st",
          "fence+syncwarp+arrive", "d_full wait", "epilogue"]
-mnames = ["d_empty wait", "b_full wait", "a_full wait", "votes + ring advance", "issue polls", "elect + 4 MMA issue", "commit", "syncwarp"]
+mnames = ["d_empty wait", "b_full wait", "a_full wait", "polls + issue + commit + votes"]
 for it in range(3):
     api._check(lib.mb200_dgemm_compressed_device(0, h, ncol, C.c_void_p(B.data_ptr()), snps,
                                                  C.c_void_p(Cn.data_ptr()), indiv), "dgemm")
     ms = C.c_float()
     lib.mb200_dgemm_last_kernel_ms(h, C.byref(ms))
-    out = (C.c_longlong * (32 + 5 * 256))()
-    lib.mb200_debug_read_trace(out, 32 + 5 * 256)
+    out = (C.c_longlong * 32)()
+    lib.mb200_debug_read_trace(out, 32)
 nchunks_cta = (snps + 511) // 512 * ((indiv + 511) // 512) / 148
 slots = nchunks_cta * 4  # per expander group
 tot = sum(out[i] for i in range(8))
 print(f"kernel {ms.value:.3f} ms; expander warp 0 total {tot} cycles; ~{slots:.0f} slots per group")
 for i, n in enumerate(names):
     print(f"  {n:28s} {out[i]:12d}  {100*out[i]/tot:5.1f}%  {out[i]/slots:8.1f} cyc/slot")
-mt = sum(out[16 + i] for i in range(8))
-print(f"MMA warp total {mt} cycles; {slots*4:.0f} slots")
+mt = sum(out[16 + i] for i in range(4))
+print(f"MMA warp (group 0) total {mt} cycles; {slots:.0f} slots")
 for i, n in enumerate(mnames):
-    print(f"  {n:28s} {out[16+i]:12d}  {100*out[16+i]/mt:5.1f}%  {out[16+i]/(slots*4):8.1f} cyc/slot")
+    print(f"  {n:28s} {out[16+i]:12d}  {100*out[16+i]/mt:5.1f}%  {out[16+i]/slots:8.1f} cyc/slot")
 lib.free_compressed(C.byref(h))
 
-if os.environ.get("MB200_BRIEF"):
-    sys.exit(0)
-ev = [[out[32 + k * 256 + i] for i in range(256)] for k in range(5)]
-base = min(x for x in ev[2] if x > 0)
-print("slot  grp | exp:a_empty_pass  a_full_arrive | mma:a_full_pass  issue_done   (cycles rel.)  [expander events only from warp 0 of each group]")
-for i in range(96):
-    print(f"{i:4d}  g{i%4} | {ev[0][i]-base:8d} {ev[1][i]-base:8d} | {ev[2][i]-base:8d} {ev[3][i]-base:8d}   dMMA={ev[3][i]-ev[3][i-1] if i else 0}")
-print("z_full pass times (chunk*16+g):", [(i, ev[4][i]-base) for i in range(0, 96) if ev[4][i] > 0])
