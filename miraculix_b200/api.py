@@ -67,7 +67,7 @@ def load_library(path: str | None = None):
     global _LIB
     if _LIB is not None and path is None:
         return _LIB
-    path = path or LIB_PATH
+    path = path or os.environ.get("MB200_LIB_PATH") or LIB_PATH  # env override: A/B kernel builds
     if not os.path.exists(path):
         raise RuntimeError(f"{path} not built: run `python -m miraculix_b200.build` "
                            "(there is no CPU fallback)")

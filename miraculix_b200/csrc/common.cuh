@@ -89,6 +89,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking probe of a phase (test_wait never suspends the thread; try_wait may, until the
+// phase completes or a time limit passes -- which stalls everything issued after it).
+__device__ __forceinline__ bool mbar_test_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Bounded wait: a protocol bug traps (kernel error returned to the host) instead of hanging
 // the GPU box; the bound is wall-clock (%globaltimer), far beyond any legitimate wait here.
 __device__ __forceinline__ uint64_t global_timer_ns() {

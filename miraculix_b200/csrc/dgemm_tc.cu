@@ -249,15 +249,15 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
           if (!a_ready) mbar_wait_warp(&af[as], aph);
           tc_fence_after();
           DT_SEG(2)
-          // a try_wait costs ~90 cycles even on a completed barrier: poll the NEXT slots now and
-          // consume the answers after this slot's MMAs are issued
+          // a try_wait costs ~90 cycles even on a completed barrier: probe the NEXT slots now
+          // (test_wait: non-blocking) and consume the answers after this slot's MMAs are issued
           const int as_n = as ^ 1;
           const uint32_t aph_n = as ? aph ^ 1 : aph;
-          const bool a_poll = (p.flags & 1) ? false : mbar_try_wait(&af[as_n], aph_n);
+          const bool a_poll = (p.flags & 1) ? false : mbar_test_wait(&af[as_n], aph_n);
           const int bs_n = bs + 1 == DT_BSLOTS ? 0 : bs + 1;
           const uint32_t bph_n = bs + 1 == DT_BSLOTS ? bph ^ 1 : bph;
           bool b_poll = false;
-          if ((sub & 1) && !(p.flags & 1)) b_poll = mbar_try_wait(&b_full[bs_n], bph_n);
+          if ((sub & 1) && !(p.flags & 1)) b_poll = mbar_test_wait(&b_full[bs_n], bph_n);
           if (elect_one()) {
             const uint32_t a_tmem = tmem_base + acol0 + (g * DT_ASLOTS + as) * 32;
 #pragma unroll
