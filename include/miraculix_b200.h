@@ -80,8 +80,11 @@ int mb200_last_status(void);
 const char *mb200_last_message(void);
 /* Number of kernels this library has launched since load (bench.py "gpu_launches"). */
 unsigned long long mb200_kernel_launches(void);
-/* 0: fp64 SIMT streaming kernel.  1: exact int8-slice tcgen05 kernel (default when built).
- * slices: number of 8-bit digits each column of B is split into (5..8, default 7). */
+/* 0: fp64 SIMT streaming kernel.  1: exact int8-slice tcgen05 kernel (default).
+ * slices: number of 8-bit digits each column of B is split into: 3..8 fixed, 0 (default) =
+ * adaptive: 6 digits, checked after the product against the rigorous bound
+ *   rowsum_max * 2^(e_c - 47) <= 5e-11 * max_r |C[r,c]|   for every column c
+ * and recomputed with 8 digits (error <= 2^-62 relative to max|B_c|) when the bound fails. */
 int mb200_set_dgemm_mode(int mode, int slices);
 /* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct (default). */
 int mb200_set_crossprod_mode(int mode);
@@ -98,6 +101,10 @@ int mb200_dgemm_last_kernel_ms(void *compressed, float *ms);
  * handle, oldest first (at most 128 are kept); trans[j] (optional) = direction of call j.
  * Synchronises the stream.  Returns the number of entries written, or a negative status. */
 int mb200_dgemm_kernel_times(void *compressed, int last, float *ms, int *trans);
+/* Precision of the last tensor-core dgemm_compressed on this handle: returns 0 = fixed digit
+ * count, 1 = adaptive and the 6-digit product passed its bound, 2 = adaptive and redone with 8
+ * digits; *slices = digits of the result.  Synchronises the stream. */
+int mb200_dgemm_last_precision(void *compressed, int *slices);
 int mb200_sync(void *compressed);
 /* Developer aid: with MB200_TRACE=1 the tensor-core dgemm kernel accumulates clock64() segments
  * of one expander warp ([0..7]) and of the MMA warp ([16..19]) of CTA 0; this reads them. */

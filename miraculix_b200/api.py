@@ -45,6 +45,7 @@ SIGNATURES = {
                                                 C.c_void_p, C.c_long]),
     "mb200_stream": (C.c_void_p, [C.c_void_p]),
     "mb200_sync": (C.c_int, [C.c_void_p]),
+    "mb200_dgemm_last_precision": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "mb200_debug_read_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "mb200_dgemm_last_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "mb200_dgemm_kernel_times": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float),

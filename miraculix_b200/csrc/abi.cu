@@ -169,7 +169,7 @@ static int create_handle(long snps, long indiv, int max_n, Handle **out) {
   H_CUDA(cudaMalloc(&h->d_counts, sizeof(unsigned long long) * snps));
   H_CUDA(cudaMalloc(&h->d_B, sizeof(double) * mx * max_n));
   H_CUDA(cudaMalloc(&h->d_C, sizeof(double) * mx * max_n));
-  H_CUDA(cudaMalloc(&h->d_w, sizeof(double) * 4 * (max_n + 16)));
+  H_CUDA(cudaMalloc(&h->d_w, sizeof(double) * 8 * (max_n + 16)));
   H_CUDA(cudaMemsetAsync(h->d_snp_major, 0, (size_t)snps * h->pitch_s, h->stream));
   H_CUDA(cudaMemsetAsync(h->d_indiv_major, 0, (size_t)indiv * h->pitch_i, h->stream));
   H_CUDA(cudaMemsetAsync(h->d_counts, 0, sizeof(unsigned long long) * snps, h->stream));
@@ -224,7 +224,7 @@ unsigned long long mb200_kernel_launches(void) { return g_kernel_launches.load()
 int mb200_set_dgemm_mode(int mode, int slices) {
   Options &o = options();
   if (mode == 0 || mode == 1) o.dgemm_mode = mode;
-  if (slices >= 3 && slices <= 8) o.dgemm_slices = slices;
+  if (slices == 0 || (slices >= 3 && slices <= 8)) o.dgemm_slices = slices;
   return 0;
 }
 int mb200_set_crossprod_mode(int mode) {
@@ -286,6 +286,7 @@ int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long 
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
   }
+  if (!rc) rc = rowsum_maxima(h);
   if (rc) { destroy_handle(h); return rc; }
   *compressed = h;
   return 0;
@@ -308,6 +309,7 @@ void plink2compressed(char *plink, char *plink_transposed, int snps, int indiv, 
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
   }
+  if (!rc) rc = rowsum_maxima(h);
   if (rc) { destroy_handle(h); return; }
   if (print_level() > 0)
     printf("miraculix_b200: %d SNPs x %d individuals resident on device %d (%.1f MB)\n", snps,
@@ -357,6 +359,11 @@ int mb200_debug_read_trace(long long *out, int n) {
   clear_status();
   cudaDeviceSynchronize();
   return dgemm_tc_read_trace(out, n);
+}
+int mb200_dgemm_last_precision(void *compressed, int *slices) {
+  Handle *h = as_handle(compressed);
+  if (!h) return -1;
+  return dgemm_tc_last_precision(h, slices);
 }
 int mb200_sync(void *compressed) {
   Handle *h = as_handle(compressed);

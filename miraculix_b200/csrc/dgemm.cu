@@ -22,7 +22,8 @@ bool dgemm_tc_available();
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 center_w_kernel(const double *__restrict__ B, long ldb, long k, const double *__restrict__ x,
-                double *__restrict__ w) {
+                double *__restrict__ w, const int *__restrict__ guard) {
+  if (guard && *guard == 0) return;  // precision fallback not needed (dgemm_tc.cu)
   const int col = blockIdx.x;
   const double *b = B + (size_t)col * ldb;
   double acc = 0.0;
@@ -40,7 +41,8 @@ center_w_kernel(const double *__restrict__ B, long ldb, long k, const double *__
 }
 __global__ void __launch_bounds__(256)
 init_c_kernel(double *__restrict__ C, long ldc, long m, int n, const double *__restrict__ w,
-              const double *__restrict__ y, int centered) {
+              const double *__restrict__ y, int centered, const int *__restrict__ guard) {
+  if (guard && *guard == 0) return;
   const long r = (long)blockIdx.x * 256 + threadIdx.x;
   if (r >= m) return;
   const double yr = y ? y[r] : 1.0;
@@ -48,19 +50,19 @@ init_c_kernel(double *__restrict__ C, long ldc, long m, int n, const double *__r
 }
 
 int dgemm_center_init(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
-                      long ldc, int centered) {
+                      long ldc, int centered, double *w, const int *guard) {
   const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
   if (centered) {
-    MB_CUDA(cudaMemsetAsync(h->d_w, 0, sizeof(double) * n, h->stream));
+    MB_CUDA(cudaMemsetAsync(w, 0, sizeof(double) * n, h->stream));
     int ysplit = (int)(ceil_div(k, 256 * 16) < 64 ? ceil_div(k, 256 * 16) : 64);
     if (ysplit < 1) ysplit = 1;
     center_w_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dB, ldb, k, trans ? nullptr : h->d_f,
-                                                             h->d_w);
+                                                             w, guard);
     count_launch();
     MB_LAUNCH_CHECK();
   }
   init_c_kernel<<<(unsigned)ceil_div(m, 256), 256, 0, h->stream>>>(
-      dC, ldc, m, n, h->d_w, trans ? h->d_f : nullptr, centered);
+      dC, ldc, m, n, w, trans ? h->d_f : nullptr, centered, guard);
   count_launch();
   MB_LAUNCH_CHECK();
   return 0;
@@ -183,7 +185,7 @@ int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double
   const Options &o = options();
   if (o.dgemm_mode == 1 && dgemm_tc_available())
     return dgemm_tc_device(h, trans, n, dB, ldb, dC, ldc);
-  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered));
+  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered, h->d_w, nullptr));
   const int ev = (int)(h->ev_count % Handle::kEvRing);
   h->ev_trans[ev] = trans;
   MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));

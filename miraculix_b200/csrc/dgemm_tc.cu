@@ -31,7 +31,7 @@ namespace mb200 {
 int make_tmap_u8_2d(CUtensorMap *map, const void *base, long row_bytes, long rows, long pitch,
                     int box_bytes, int box_rows, int swizzle128);
 int dgemm_center_init(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
-                      long ldc, int centered);
+                      long ldc, int centered, double *w, const int *guard);
 
 bool dgemm_tc_available() { return true; }
 
@@ -39,7 +39,9 @@ bool dgemm_tc_available() { return true; }
 // pre-pass: per-column amax and digit slicing
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-colmax_kernel(const double *__restrict__ B, long ldb, long k, unsigned long long *__restrict__ amax) {
+colmax_kernel(const double *__restrict__ B, long ldb, long k, unsigned long long *__restrict__ amax,
+              const int *__restrict__ guard) {
+  if (guard && *guard == 0) return;
   const int col = blockIdx.x;
   const double *b = B + (size_t)col * ldb;
   double m = 0.0;
@@ -55,7 +57,8 @@ colmax_kernel(const double *__restrict__ B, long ldb, long k, unsigned long long
 __global__ void __launch_bounds__(256)
 quantize_kernel(const double *__restrict__ B, long ldb, long k, int ncols, int S,
                 const unsigned long long *__restrict__ amax, int8_t *__restrict__ Bq, long kpitch,
-                int *__restrict__ exps) {
+                int *__restrict__ exps, const int *__restrict__ guard) {
+  if (guard && *guard == 0) return;
   const long j = (long)blockIdx.x * 256 + threadIdx.x;
   const int P = 8 * S - 2;
   for (int c = 0; c < ncols; c++) {
@@ -120,6 +123,7 @@ struct DtParams {
   const int *exps;      // e_c per column
   int dbg;              // TRACE builds only: 1 skip tcgen05.st, 2 skip MMAs
   int flags;            // MB200_TC_FLAGS: 1 = no look-ahead barrier polls in the MMA warps
+  const int *guard;     // optional: run only if *guard != 0 (precision fallback pass)
 };
 
 // Optional cycle accounting (MB200_TRACE=1): CTA 0 accumulates clock64() segments of expander
@@ -163,6 +167,7 @@ template <bool TRACE>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
                 const __grid_constant__ CUtensorMap tmap_b, const DtParams p) {
+  if (p.guard && *p.guard == 0) return;  // uniform over the grid
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
@@ -423,51 +428,58 @@ static int ensure_bq(Handle *h) {
   return 0;
 }
 
-int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc) {
+// A-posteriori check of the digit count: the quantisation error of column c is at most
+// rowsum_max * 2^(e_c - P - 1) in every row; it must stay below tol * max_r |C[r,c]|.
+__global__ void decide_kernel(const unsigned long long *__restrict__ amaxB,
+                              const int *__restrict__ exps,
+                              const unsigned long long *__restrict__ amaxC, int n, int P,
+                              double rowsum_max, double tol, int *__restrict__ flag) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n || amaxB[c] == 0ull) return;  // zero column of B: exact
+  const double err = scalbn(rowsum_max, exps[c] - P - 1);
+  const double mc = __longlong_as_double((long long)amaxC[c]);
+  if (!(err <= tol * mc)) atomicOr(flag, 1);
+}
+
+// Scratch inside d_w (8 M doubles, M = max_n + 16), one set per pass so that the guarded
+// fallback pass never races with the first one.
+struct TcScratch {
+  double *w;
+  unsigned long long *amaxB;
+  int *exps;
+};
+static TcScratch tc_scratch(Handle *h, int set) {
+  const long M = h->max_n + 16;
+  double *base = h->d_w + (set ? 4 * M : 0);
+  return {base, reinterpret_cast<unsigned long long *>(base + M), reinterpret_cast<int *>(base + 2 * M)};
+}
+
+// One full product at S digits per column: centre-init of C, then per column group
+// colmax -> quantize -> main kernel.  guard != nullptr: every kernel is a no-op unless *guard.
+static int tc_pass(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc,
+                   int S, int set, const int *guard, bool trace, bool *first_main, int ev) {
   const Options &o = options();
-  int S = o.dgemm_slices;
-  if (S < 3) S = 3;
-  if (S > 8) S = 8;
   const uint8_t *Z = trans ? h->d_snp_major : h->d_indiv_major;
   const long pitch = trans ? h->pitch_s : h->pitch_i;
   const long rows = trans ? h->snps : h->indiv, K = trans ? h->indiv : h->snps;
   const long kpitch = pitch * 4;
-  MB_CHECK(ensure_bq(h));
-  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered));
-
-  // scratch inside d_w (4 * (max_n + 16) doubles): [0, max_n) centring, then amax bits, exponents
-  unsigned long long *d_amax = reinterpret_cast<unsigned long long *>(h->d_w + (h->max_n + 16));
-  int *d_exps = reinterpret_cast<int *>(h->d_w + 2 * (h->max_n + 16));
-
-  static bool attr_set = false;
-  static bool trace = false;
-  if (!attr_set) {
-    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 dt_smem_bytes(DT_NMAX)));
-    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 dt_smem_bytes(DT_NMAX)));
-    const char *e = getenv("MB200_TRACE");
-    trace = e && atoi(e) > 0;
-    attr_set = true;
-  }
+  const TcScratch sc = tc_scratch(h, set);
+  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered, sc.w, guard));
   CUtensorMap tz;
   MB_CHECK(make_tmap_u8_2d(&tz, Z, pitch, rows, pitch, 128, 128, 1));
+  MB_CUDA(cudaMemsetAsync(sc.amaxB, 0, sizeof(unsigned long long) * n, h->stream));
 
   const int cpp = DT_NMAX / S;  // columns per pass
-  const int ev = (int)(h->ev_count % Handle::kEvRing);
-  h->ev_trans[ev] = trans;
-  bool first = true;
   for (int c0 = 0; c0 < n; c0 += cpp) {
     const int nc = n - c0 < cpp ? n - c0 : cpp;
     const int N = (int)round_up((long)nc * S, 16);
     const double *B = dB + (size_t)c0 * ldb;
-    MB_CUDA(cudaMemsetAsync(d_amax, 0, sizeof(unsigned long long) * nc, h->stream));
     int ysplit = (int)ceil_div(K, 256 * 32);
     if (ysplit > 128) ysplit = 128;
     if (ysplit < 1) ysplit = 1;
-    colmax_kernel<<<dim3(nc, ysplit), 256, 0, h->stream>>>(B, ldb, K, d_amax);
-    quantize_kernel<<<(unsigned)ceil_div(K, 256), 256, 0, h->stream>>>(B, ldb, K, nc, S, d_amax,
-                                                                        h->d_Bq, kpitch, d_exps);
+    colmax_kernel<<<dim3(nc, ysplit), 256, 0, h->stream>>>(B, ldb, K, sc.amaxB + c0, guard);
+    quantize_kernel<<<(unsigned)ceil_div(K, 256), 256, 0, h->stream>>>(
+        B, ldb, K, nc, S, sc.amaxB + c0, h->d_Bq, kpitch, sc.exps + c0, guard);
     count_launch(2);
     MB_LAUNCH_CHECK();
 
@@ -489,22 +501,90 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
     p.ncols = nc;
     p.C = dC + (size_t)c0 * ldc;
     p.ldc = ldc;
-    p.exps = d_exps;
+    p.exps = sc.exps + c0;
+    p.guard = guard;
     p.dbg = 0;
     { static int fl = -1; if (fl < 0) { const char *e = getenv("MB200_TC_FLAGS"); fl = e ? atoi(e) : 0; } p.flags = fl; }
     if (trace) { const char *e = getenv("MB200_DBG"); p.dbg = e ? atoi(e) : 0; }
     const long units = (long)p.row_blocks * p.ksplits;
     const int grid = (int)(units < h->sm_count ? units : h->sm_count);
-    if (first) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
-    first = false;
+    if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
+    *first_main = false;
     if (trace) dgemm_tc_kernel<true><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
     else dgemm_tc_kernel<false><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
     count_launch();
     MB_LAUNCH_CHECK();
   }
+  return 0;
+}
+
+int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc) {
+  const Options &o = options();
+  MB_CHECK(ensure_bq(h));
+  static bool attr_set = false;
+  static bool trace = false;
+  static double tol = 5e-11;
+  if (!attr_set) {
+    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 dt_smem_bytes(DT_NMAX)));
+    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 dt_smem_bytes(DT_NMAX)));
+    const char *e = getenv("MB200_TRACE");
+    trace = e && atoi(e) > 0;
+    if (const char *t = getenv("MB200_DGEMM_TOL")) tol = atof(t) > 0 ? atof(t) : tol;
+    attr_set = true;
+  }
+  const long rows = trans ? h->snps : h->indiv, K = trans ? h->indiv : h->snps;
+  const int ev = (int)(h->ev_count % Handle::kEvRing);
+  h->ev_trans[ev] = trans;
+  bool first_main = true;
+
+  // Digit count.  Fixed (3..8) when asked for; otherwise adaptive: 8 digits where they cost
+  // nothing (n <= 2 fills one 16-row MMA either way; small problems), else 6 digits, verified
+  // against a rigorous bound and redone with 8 digits by guarded kernels if the bound fails.
+  int S = o.dgemm_slices;
+  bool adaptive = false;
+  if (S == 0) {
+    if (n <= 2 || (double)rows * (double)K < 268435456.0) S = 8;
+    else { S = 6; adaptive = true; }
+  }
+  if (S < 3) S = 3;
+  if (S > 8) S = 8;
+  h->last_slices = S;
+  h->last_adaptive = adaptive;
+  int *d_flag = reinterpret_cast<int *>(h->d_w + 8 * (h->max_n + 16) - 1);
+  MB_CHECK(tc_pass(h, trans, n, dB, ldb, dC, ldc, S, 0, nullptr, trace, &first_main, ev));
+  if (adaptive) {
+    const TcScratch sc = tc_scratch(h, 0);
+    unsigned long long *amaxC = reinterpret_cast<unsigned long long *>(h->d_w + 3 * (h->max_n + 16));
+    MB_CUDA(cudaMemsetAsync(amaxC, 0, sizeof(unsigned long long) * n, h->stream));
+    MB_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(int), h->stream));
+    int ysplit = (int)ceil_div(rows, 256 * 32);
+    if (ysplit > 128) ysplit = 128;
+    if (ysplit < 1) ysplit = 1;
+    colmax_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dC, ldc, rows, amaxC, nullptr);
+    decide_kernel<<<(unsigned)ceil_div(n, 64), 64, 0, h->stream>>>(
+        sc.amaxB, sc.exps, amaxC, n, 8 * S - 2, h->rowsum_max[trans ? 1 : 0], tol, d_flag);
+    count_launch(2);
+    MB_LAUNCH_CHECK();
+    MB_CHECK(tc_pass(h, trans, n, dB, ldb, dC, ldc, 8, 1, d_flag, trace, &first_main, ev));
+  }
   MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
   h->ev_count++;
   return 0;
+}
+
+// 0: fixed digit count was used; 1: adaptive, 6 digits passed the bound; 2: adaptive, redone with 8
+int dgemm_tc_last_precision(Handle *h, int *slices) {
+  if (slices) *slices = h->last_slices;
+  if (!h->last_adaptive) return 0;
+  int flag = 0;
+  int *d_flag = reinterpret_cast<int *>(h->d_w + 8 * (h->max_n + 16) - 1);
+  if (cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+      cudaStreamSynchronize(h->stream) != cudaSuccess)
+    return -1;
+  if (flag && slices) *slices = 8;
+  return flag ? 2 : 1;
 }
 
 int dgemm_tc_read_trace(long long *out, int n) {

@@ -15,7 +15,7 @@ struct Options {
   int print_details = 0;
   int variant = 256;
   int dgemm_mode = 1;      // 0 fp64 SIMT, 1 int8-slice tcgen05
-  int dgemm_slices = 7;    // 8-bit digits per column of B in mode 1
+  int dgemm_slices = 0;    // 8-bit digits per column of B in mode 1; 0 = adaptive (6, verified, else 8)
   int crossprod_mode = 1;  // 0 dp4a SIMT, 1 tcgen05
 };
 Options &options();
@@ -43,7 +43,10 @@ struct Handle {
   // per-call scratch, sized for max_n columns, allocated once (no per-call malloc):
   double *d_B = nullptr;   // [max(snps,indiv)] x max_n, ld = rows of B
   double *d_C = nullptr;   // [max(snps,indiv)] x max_n
-  double *d_w = nullptr;   // centring scalars / column scales, 4*max_n doubles
+  double *d_w = nullptr;   // centring scalars, column maxima, exponents, flag: 8 (max_n + 16) doubles
+  int last_slices = 0;            // digits used by the last tensor-core dgemm on this handle
+  bool last_adaptive = false;
+  double rowsum_max[2] = {0, 0};  // max_r sum_k z_rk of the indiv-major / snp-major layout
   int8_t *d_Bq = nullptr;  // sliced int8 panel for the tensor-core path
   size_t bq_bytes = 0;
   void *pinned = nullptr;  // pinned staging for host<->device copies of B / C
@@ -65,11 +68,13 @@ int repack_from_device(Handle *h, const uint8_t *d_plink);  // d_plink: [snps][c
 int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long seed,
                    cudaStream_t stream);
 int freq_from_counts(Handle *h);  // d_f = counts / (2 indiv)
+int rowsum_maxima(Handle *h);     // fills h->rowsum_max (synchronises the stream)
 
 // dgemm.cu
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
 
-int dgemm_tc_read_trace(long long *out, int n);  // dgemm_tc.cu, MB200_TRACE=1
+int dgemm_tc_read_trace(long long *out, int n);
+int dgemm_tc_last_precision(Handle *h, int *slices);  // dgemm_tc.cu, MB200_TRACE=1
 
 // crossprod.cu
 struct CrossprodTiming {

@@ -131,6 +131,45 @@ int freq_from_counts(Handle *h) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// max_r sum_k z_rk of one device orientation: the rigorous error bound of the digit-sliced
+// tensor-core dgemm (dgemm_tc.cu) needs it.  One warp per row, HBM-bound, once per handle.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rowsum_max_kernel(const uint8_t *__restrict__ A, long pitch, long rows, unsigned int *__restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const long warp0 = (long)blockIdx.x * 8 + (threadIdx.x >> 5), nwarps = (long)gridDim.x * 8;
+  unsigned int best = 0;
+  for (long r = warp0; r < rows; r += nwarps) {
+    const uint4 *row = reinterpret_cast<const uint4 *>(A + r * pitch);
+    unsigned int acc = 0;
+    for (long i = lane; i < pitch / 16; i += 32) {
+      const uint4 v = __ldg(row + i);
+      acc += __popc(v.x & 0x55555555u) + 2 * __popc(v.x & 0xAAAAAAAAu) +
+             __popc(v.y & 0x55555555u) + 2 * __popc(v.y & 0xAAAAAAAAu) +
+             __popc(v.z & 0x55555555u) + 2 * __popc(v.z & 0xAAAAAAAAu) +
+             __popc(v.w & 0x55555555u) + 2 * __popc(v.w & 0xAAAAAAAAu);
+    }
+    acc = __reduce_add_sync(0xffffffffu, acc);
+    best = acc > best ? acc : best;
+  }
+  if (lane == 0 && best) atomicMax(out, best);
+}
+int rowsum_maxima(Handle *h) {
+  unsigned int *d = reinterpret_cast<unsigned int *>(h->d_w);  // scratch, free at creation time
+  unsigned int host[2] = {0, 0};
+  MB_CUDA(cudaMemsetAsync(d, 0, 2 * sizeof(unsigned int), h->stream));
+  rowsum_max_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_indiv_major, h->pitch_i, h->indiv, d);
+  rowsum_max_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_snp_major, h->pitch_s, h->snps, d + 1);
+  count_launch(2);
+  MB_LAUNCH_CHECK();
+  MB_CUDA(cudaMemcpyAsync(host, d, sizeof(host), cudaMemcpyDeviceToHost, h->stream));
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  h->rowsum_max[0] = host[0];
+  h->rowsum_max[1] = host[1];
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // On-device simulator (benchmark inputs): p_j ~ U(0.1,0.6),
 // z_ij ~ Binomial(2,p_j) = [u1<p] + [u2<p], PLINK codes 0->00, 1->10, 2->11, pad bits 00.
 // Counter-based: every genotype is a pure function of (seed, snp, indiv).

@@ -52,16 +52,19 @@ def test_repack_bit_exact(gpu_lib, snps, indiv, missing):
     assert not h.value  # free_compressed nulls the caller's pointer
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+MODES = [(0, 7), (1, 7), (1, 6), (1, 8), (1, 0)]  # (kernel family, digits; 0 = adaptive)
+
+
+@pytest.mark.parametrize("mode,slices", MODES)
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "dgemm_*.npz"))))
-def test_dgemm_matches_reference_golden(gpu_lib, path, mode):
+def test_dgemm_matches_reference_golden(gpu_lib, path, mode, slices):
     """Outputs of the unmodified reference CPU 5codes library on the same inputs."""
     from miraculix_b200 import api
     g = np.load(path)
     centered = path.endswith("_c1.npz")
     snps, indiv = int(g["snps"]), int(g["indiv"])
     api.set_options(use_gpu=True, not_center=not centered)
-    gpu_lib.mb200_set_dgemm_mode(mode, 7)
+    gpu_lib.mb200_set_dgemm_mode(mode, slices)
     h = api.init_compressed(g["plink"], snps, indiv, g["f"], 16)
     try:
         for tr in "NT":
@@ -69,17 +72,17 @@ def test_dgemm_matches_reference_golden(gpu_lib, path, mode):
             assert relerr(Cg, g[f"C_{tr}"]) <= TOL, (os.path.basename(path), tr, mode)
     finally:
         api.free_compressed(h)
-        gpu_lib.mb200_set_dgemm_mode(1, 7)
+        gpu_lib.mb200_set_dgemm_mode(1, 0)
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode,slices", MODES)
 @pytest.mark.parametrize("snps,indiv,ncol", [(10000, 1000, 1), (1003, 203, 10), (2051, 777, 3),
                                              (512, 128, 16), (4097, 2050, 7)])
-def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode):
+def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode, slices):
     from miraculix_b200 import api
     plink, Z, f = simulate.simulate(snps, indiv, seed=snps + ncol, missing=0.01)
     rng = np.random.default_rng(ncol)
-    gpu_lib.mb200_set_dgemm_mode(mode, 7)
+    gpu_lib.mb200_set_dgemm_mode(mode, slices)
     h = api.init_compressed(plink, snps, indiv, f, ncol)
     try:
         for tr, k in (("N", snps), ("T", indiv)):
@@ -88,7 +91,36 @@ def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode):
             assert relerr(api.dgemm_compressed(tr, h, B, snps, indiv), want) <= TOL, (tr, mode)
     finally:
         api.free_compressed(h)
-        gpu_lib.mb200_set_dgemm_mode(1, 7)
+        gpu_lib.mb200_set_dgemm_mode(1, 0)
+
+
+def test_dgemm_adaptive_precision(gpu_lib):
+    """Default digit policy on a problem large enough to take the 6-digit path: the verified
+    product meets the 1e-10 bar (precision code 1); a product that cancels to ~0 (centred 'T'
+    times the ones vector: Z^T 1 - 2 f indiv = 0) fails the bound and is redone with 8 digits
+    (code 2), still matching the oracle to 1e-10 of the uncancelled magnitude."""
+    from miraculix_b200 import api
+    snps, indiv, ncol = 16384, 20000, 3
+    plink, Z, f = simulate.simulate(snps, indiv, seed=99)
+    rng = np.random.default_rng(100)
+    gpu_lib.mb200_set_dgemm_mode(1, 0)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    sl = C.c_int(0)
+    try:
+        for tr, k in (("N", snps), ("T", indiv)):
+            B = np.asfortranarray(rng.standard_normal((k, ncol)))
+            got = api.dgemm_compressed(tr, h, B, snps, indiv)
+            assert gpu_lib.mb200_dgemm_last_precision(h, C.byref(sl)) == 1 and sl.value == 6
+            want = cport.dgemm_compressed(tr, plink, snps, indiv, f, B, True)
+            assert relerr(got, want) <= TOL, tr
+        ones = np.ones((indiv, ncol), order="F")
+        got = api.dgemm_compressed("T", h, ones, snps, indiv)
+        assert gpu_lib.mb200_dgemm_last_precision(h, C.byref(sl)) == 2 and sl.value == 8
+        want = cport.dgemm_compressed("T", plink, snps, indiv, f, ones, True)
+        scale = float(Z.sum(axis=0).max())  # magnitude of the two terms that cancel
+        assert np.abs(got - want).max() <= TOL * scale
+    finally:
+        api.free_compressed(h)
 
 
 def test_dgemm_leading_dimensions_and_max_n(gpu_lib):
