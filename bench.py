@@ -287,10 +287,21 @@ def run_ours(args):
     h2d = 8 * ncol * (s_loc + indiv)
     d2h = 8 * ncol * (indiv + s_loc)
 
+    # Tear down in an order that never leaves torch holding events on the library's stream:
+    # pinned and device panels first (the host allocator records an event on every stream that
+    # used a pinned block), then the process group, then the handle (which destroys the stream).
+    del hBn, hBt, hCn, hCt, Bn, Bt, Cn, Ct
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    if hasattr(torch._C, "_host_emptyCache"):
+        torch._C._host_emptyCache()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sh._stream = None
+    del stream
+    lib.free_compressed(C.byref(handle))
     if rank != 0:
-        lib.free_compressed(C.byref(handle))
-        if world > 1:
-            dist.destroy_process_group()
         return
 
     hbm, _bf16, peak_src = peaks()
@@ -334,10 +345,6 @@ def run_ours(args):
                            "ShardedCompressed with pinned host B/C + NCCL all-reduce"},
             "gpu_launches": int(launches), "clocks": clocks}
 
-    lib.free_compressed(C.byref(handle))
-    del Bn, Bt, Cn, Ct
-    torch.cuda.empty_cache()
-
     if not args.no_grm and world == 1:
         line["grm"] = run_grm(args, lib, api, dev)
     if not args.no_cpu:
@@ -346,8 +353,6 @@ def run_ours(args):
         except Exception as exc:  # the CPU checker must never take the GPU line down
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                                     "sample": f"failed: {exc}"}
-    if world > 1:
-        dist.destroy_process_group()
     print(json.dumps(line))
 
 

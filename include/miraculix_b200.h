@@ -148,6 +148,20 @@ int mb200_grm(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool 
               const double *f, bool do_scale);
 int mb200_ld(unsigned char *snp_matrix, int snps, int indiv, double *ans, bool is_plink_format,
              const double *f);
+/* 2-D output-tile partition of the crossproduct over GPUs (no communication):
+ * partition `part` of `nparts` owns the 128-row tiles t with t % nparts == part.  The panel is
+ * compact and row-major, [mb200_crossprod_partition_rows(rows, part, nparts)][rows] doubles; local
+ * row lr is global row i = ((lr/128) nparts + part) 128 + lr%128; entries with column
+ * j < 256 floor(i/256) (strictly left of the diagonal tile) are not computed and read 0 -- use
+ * symmetry.  mode 0: raw counts; mode 1: centred (and scaled) GRM, crossproduct.jl:91-106, with
+ * the row sums obtained exactly from the input (m = X X^T 1), so ranks never exchange data.
+ * d_x: the FULL packed matrix [rows][ceil(k/4)], replicated on every GPU. */
+long mb200_crossprod_partition_rows(long rows, int part, int nparts);
+int mb200_crossprod_partition_device(const unsigned char *d_x, long k, long rows, int is_plink_format,
+                                     int mode, const double *d_f, int do_scale, int part, int nparts,
+                                     double *d_panel);
+int mb200_grm_partition(unsigned char *snp_matrix, int snps, int indiv, bool is_plink_format, int mode,
+                        const double *f, bool do_scale, int part, int nparts, double *panel);
 /* Timing of the device part of the last crossproduct call on this thread, in milliseconds:
  * [0] expand+GEMM, [1] epilogue (int32 -> fp64, symmetrise, centre), [2] executed int8 ops. */
 int mb200_crossprod_last_timing(double out[3]);

@@ -59,6 +59,11 @@ SIGNATURES = {
                                          C.c_void_p, C.c_int, C.c_void_p]),
     "mb200_grm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool, C.c_void_p, C.c_bool]),
     "mb200_ld": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool, C.c_void_p]),
+    "mb200_crossprod_partition_rows": (C.c_long, [C.c_long, C.c_int, C.c_int]),
+    "mb200_crossprod_partition_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_int,
+                                                   C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "mb200_grm_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_bool, C.c_int, C.c_void_p,
+                                      C.c_bool, C.c_int, C.c_int, C.c_void_p]),
     "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
 }
 
@@ -219,6 +224,25 @@ def ld(x: np.ndarray, snps: int, indiv: int, is_plink_format: bool = False,
                                  f.ctypes.data)
     _check(rc, "mb200_ld")
     return M
+
+
+def grm_partition(x: np.ndarray, snps: int, indiv: int, part: int, nparts: int, mode: int = 1,
+                  is_plink_format: bool = False, do_scale: bool = True,
+                  allele_freq: np.ndarray | None = None):
+    """One partition's panel of the (centred) GRM: (global_row_index[local_rows], panel[local_rows,
+    indiv]); entries left of the diagonal tile are 0 (see include/miraculix_b200.h)."""
+    x = _check_packed(x, snps, indiv)
+    lib = load_library()
+    lrows = lib.mb200_crossprod_partition_rows(indiv, part, nparts)
+    panel = np.zeros((lrows, indiv), dtype=np.float64)
+    f = np.ascontiguousarray(allele_freq, dtype=np.float64) if allele_freq is not None else None
+    if lrows:
+        rc = lib.mb200_grm_partition(x.ctypes.data, snps, indiv, is_plink_format, mode,
+                                     f.ctypes.data if f is not None else None, do_scale, part, nparts,
+                                     panel.ctypes.data)
+        _check(rc, "mb200_grm_partition")
+    lr = np.arange(lrows)
+    return ((lr // 128) * nparts + part) * 128 + lr % 128, panel
 
 
 def crossprod_last_timing():

@@ -471,6 +471,49 @@ int mb200_crossprod_device(const unsigned char *d_x, long k, long rows, int is_p
                           &t_cp_timing);
 }
 
+long mb200_crossprod_partition_rows(long rows, int part, int nparts) {
+  return crossprod_partition_rows(rows, part, nparts);
+}
+int mb200_crossprod_partition_device(const unsigned char *d_x, long k, long rows, int is_plink_format,
+                                     int mode, const double *d_f, int do_scale, int part, int nparts,
+                                     double *d_panel) {
+  clear_status();
+  return crossprod_partition_device(d_x, k, rows, is_plink_format, mode, d_f, do_scale, part, nparts,
+                                    d_panel, 0, &t_cp_timing);
+}
+// host-pointer convenience wrapper of the above (tests, small problems)
+int mb200_grm_partition(unsigned char *snp_matrix, int snps, int indiv, bool is_plink_format, int mode,
+                        const double *f, bool do_scale, int part, int nparts, double *panel) {
+  clear_status();
+  if (!snp_matrix || !panel || snps <= 0 || indiv <= 0)
+    return fail(-2, __func__, __LINE__, "bad arguments") ? 1 : 1;
+  if (select_device() < 0) return 1;
+  const long nb = ceil_div(snps, 4), lrows = crossprod_partition_rows(indiv, part, nparts);
+  if (lrows == 0) return 0;
+  uint8_t *d_x = nullptr;
+  double *d_p = nullptr, *d_f = nullptr;
+  int rc = 0;
+  cudaError_t e;
+#define P_CUDA(expr)                                                                     \
+  if (!rc && (e = (expr)) != cudaSuccess)                                                 \
+    rc = fail((int)e, __func__, __LINE__, "%s: %s", #expr, cudaGetErrorString(e))
+  P_CUDA(cudaMalloc(&d_x, (size_t)indiv * nb));
+  P_CUDA(cudaMalloc(&d_p, sizeof(double) * lrows * indiv));
+  P_CUDA(cudaMemcpy(d_x, snp_matrix, (size_t)indiv * nb, cudaMemcpyHostToDevice));
+  if (f && mode) {
+    P_CUDA(cudaMalloc(&d_f, sizeof(double) * snps));
+    P_CUDA(cudaMemcpy(d_f, f, sizeof(double) * snps, cudaMemcpyHostToDevice));
+  }
+  if (!rc) rc = crossprod_partition_device(d_x, snps, indiv, is_plink_format, mode, d_f, do_scale, part,
+                                           nparts, d_p, 0, &t_cp_timing);
+  P_CUDA(cudaMemcpy(panel, d_p, sizeof(double) * lrows * indiv, cudaMemcpyDeviceToHost));
+#undef P_CUDA
+  cudaFree(d_x);
+  cudaFree(d_p);
+  cudaFree(d_f);
+  return rc ? 1 : 0;
+}
+
 int mb200_crossprod_last_timing(double out[3]) {
   out[0] = t_cp_timing.gemm_ms;
   out[1] = t_cp_timing.epilogue_ms;

@@ -15,7 +15,8 @@
 namespace mb200 {
 
 struct TileCoord;
-int build_tile_list(long rows, TileCoord **d_tiles, int *num_tiles, cudaStream_t stream);
+int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
+                    cudaStream_t stream);
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
@@ -61,7 +62,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
   const int tc = options().crossprod_mode == 1;
-  if (tc) MB_CHECK(build_tile_list(rows, &d_tiles, &num_tiles, stream));
+  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   double executed_ops = 0.0;
@@ -116,6 +117,116 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   MB_CUDA(cudaFreeAsync(C32, stream));
   MB_CUDA(cudaFreeAsync(d_m, stream));
   if (d_tiles) MB_CUDA(cudaFreeAsync(d_tiles, stream));
+  MB_CUDA(cudaStreamSynchronize(stream));
+  if (timing) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, e0, e1);
+    cudaEventElapsedTime(&b, e1, e2);
+    timing->gemm_ms = a;
+    timing->epilogue_ms = b;
+    timing->executed_ops = executed_ops;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaEventDestroy(e2);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 2-D output-tile partition over GPUs (BASELINE configs[4]): partition `part` of
+// `nparts` owns the 128-row tiles mi with mi % nparts == part (cyclic = balanced over the upper
+// triangle) and computes them against all column tiles at or right of the diagonal.  The packed
+// input is replicated; nothing is exchanged: even the row sums the centring needs are computed
+// exactly from the input, m = X (X^T 1).  Output: compact fp64 panel [local_rows][rows].
+// ---------------------------------------------------------------------------------------------
+long crossprod_partition_rows(long rows, int part, int nparts) {
+  const long Mt = ceil_div(rows, 128);
+  const long owned = part < Mt ? ceil_div(Mt - part, nparts) : 0;
+  return owned * 128;
+}
+
+int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
+                               const double *d_f, int do_scale, int part, int nparts,
+                               double *d_panel, cudaStream_t stream, CrossprodTiming *timing) {
+  if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
+  if (nparts < 1 || part < 0 || part >= nparts)
+    return fail(-2, __func__, __LINE__, "bad partition %d of %d", part, nparts);
+  if (mode < 0 || mode > 1) return fail(-2, __func__, __LINE__, "mode %d not supported on panels", mode);
+  int device = 0;
+  MB_CUDA(cudaGetDevice(&device));
+  const int sms = device_sm_count(device);
+  const long nb = ceil_div(k, 4);
+  const long rows_pad = round_up(rows, 256);
+  const long local_rows = crossprod_partition_rows(rows, part, nparts);
+  if (local_rows == 0) return 0;
+
+  double slab_gb = 8.0;
+  if (const char *e = getenv("MB200_SLAB_GB")) slab_gb = atof(e) > 0 ? atof(e) : slab_gb;
+  long slab_kbytes = (long)(slab_gb * 1073741824.0 / (double)rows_pad) / 4 / 32 * 32;
+  if (slab_kbytes < 32) slab_kbytes = 32;
+  if (slab_kbytes > round_up(nb, 32)) slab_kbytes = round_up(nb, 32);
+  const long kpad = slab_kbytes * 4;
+  if (is_plink_format || mode) MB_CHECK(upload_lut());
+
+  int8_t *X8 = nullptr;
+  int32_t *C32 = nullptr;
+  double *d_m = nullptr;
+  unsigned long long *d_s = nullptr;
+  TileCoord *d_tiles = nullptr;
+  int num_tiles = 0;
+  cudaEvent_t e0, e1, e2;
+  MB_CUDA(cudaEventCreate(&e0));
+  MB_CUDA(cudaEventCreate(&e1));
+  MB_CUDA(cudaEventCreate(&e2));
+  MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
+  MB_CUDA(cudaMallocAsync(&C32, (size_t)local_rows * rows_pad * sizeof(int32_t), stream));
+  MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
+  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream));
+
+  MB_CUDA(cudaEventRecord(e0, stream));
+  double executed_ops = 0.0;
+  int slab = 0;
+  for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
+    const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
+    const long kuse = round_up(kbytes * 4, 128);
+    expand_2bit_kernel<<<sms * 8, 256, 0, stream>>>(d_x, rows, nb, kb0, kbytes, is_plink_format,
+                                                   X8, rows_pad, kpad);
+    count_launch();
+    MB_LAUNCH_CHECK();
+    MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
+                                 slab > 0, sms, stream));
+    executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
+  }
+  MB_CUDA(cudaEventRecord(e1, stream));
+
+  if (mode == 1) {
+    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned long long) * 4 * nb, stream));
+    MB_CUDA(cudaMemsetAsync(d_s, 0, sizeof(unsigned long long) * 4 * nb, stream));
+    int ysplit = (int)(rows / 512 < 1 ? 1 : rows / 512 > 64 ? 64 : rows / 512);
+    snp_colsum_kernel<<<dim3((unsigned)ceil_div(nb, 256), ysplit), 256, 0, stream>>>(
+        d_x, rows, nb, is_plink_format, d_s);
+    row_dot_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(d_x, rows, nb, is_plink_format,
+                                                                    d_s, d_m);
+    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
+    count_launch(3);
+    if (do_scale) {
+      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
+      count_launch();
+    }
+    MB_LAUNCH_CHECK();
+  }
+  panel_finish_kernel<<<sms * 8, 256, 0, stream>>>(C32, rows_pad, local_rows, rows, part, nparts,
+                                                   mode, d_m, d_m + rows, do_scale, d_panel);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  MB_CUDA(cudaEventRecord(e2, stream));
+
+  MB_CUDA(cudaFreeAsync(X8, stream));
+  MB_CUDA(cudaFreeAsync(C32, stream));
+  MB_CUDA(cudaFreeAsync(d_m, stream));
+  if (d_s) MB_CUDA(cudaFreeAsync(d_s, stream));
+  MB_CUDA(cudaFreeAsync(d_tiles, stream));
   MB_CUDA(cudaStreamSynchronize(stream));
   if (timing) {
     float a = 0, b = 0;

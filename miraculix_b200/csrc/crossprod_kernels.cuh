@@ -156,6 +156,74 @@ ld_scale_kernel(double *__restrict__ M, long n, const double *__restrict__ sigma
   }
 }
 
+// ---- exact row sums of M = X X^T without forming M:  m = X (X^T 1)  (used by the partitioned
+// GRM so that the centring needs no communication between the GPUs that own the output tiles)
+__device__ __forceinline__ uint32_t packed_values(uint32_t byte, int is_plink) {
+  return is_plink ? c_plink2twobit[byte] : byte;  // 4 fields, each the value 0..3
+}
+// s[4b + t] += sum_r field_t(x[r][b]);  thread = packed byte column, grid.y splits the rows
+__global__ void __launch_bounds__(256)
+snp_colsum_kernel(const uint8_t *__restrict__ x, long rows, long nb, int is_plink,
+                  unsigned long long *__restrict__ s) {
+  const long b = (long)blockIdx.x * 256 + threadIdx.x;
+  if (b >= nb) return;
+  const long per = (rows + gridDim.y - 1) / gridDim.y;
+  const long r0 = (long)blockIdx.y * per, r1 = r0 + per < rows ? r0 + per : rows;
+  unsigned int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+  for (long r = r0; r < r1; r++) {
+    const uint32_t v = packed_values(x[r * nb + b], is_plink);
+    c0 += v & 3u; c1 += (v >> 2) & 3u; c2 += (v >> 4) & 3u; c3 += (v >> 6) & 3u;
+  }
+  if (c0) atomicAdd(&s[4 * b + 0], (unsigned long long)c0);
+  if (c1) atomicAdd(&s[4 * b + 1], (unsigned long long)c1);
+  if (c2) atomicAdd(&s[4 * b + 2], (unsigned long long)c2);
+  if (c3) atomicAdd(&s[4 * b + 3], (unsigned long long)c3);
+}
+// m[r] = sum_k x_rk s_k, exact in 64-bit integers (one warp per row)
+__global__ void __launch_bounds__(256)
+row_dot_kernel(const uint8_t *__restrict__ x, long rows, long nb, int is_plink,
+               const unsigned long long *__restrict__ s, double *__restrict__ m) {
+  const long r = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  unsigned long long acc = 0;
+  for (long b = lane; b < nb; b += 32) {
+    const uint32_t v = packed_values(x[r * nb + b], is_plink);
+    acc += (v & 3u) * s[4 * b] + ((v >> 2) & 3u) * s[4 * b + 1] + ((v >> 4) & 3u) * s[4 * b + 2] +
+           ((v >> 6) & 3u) * s[4 * b + 3];
+  }
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) m[r] = (double)acc;
+}
+// Compact panel of one partition: local row lr is global row ((lr/128) nparts + part) 128 + lr%128.
+// Columns left of the first computed tile (256 floor(i/256)) are not part of the panel: zero.
+// mode 1 applies the GRM update in the operation order of crossproduct.jl:95-106.
+__global__ void __launch_bounds__(256)
+panel_finish_kernel(const int32_t *__restrict__ C32, long ld32, long local_rows, long n, int part,
+                    int nparts, int mode, const double *__restrict__ m,
+                    const double *__restrict__ scal, int do_scale, double *__restrict__ out) {
+  const long total = local_rows * n;
+  const double alpha = -1.0 / (double)n;
+  const double shift = mode ? scal[0] / ((double)n * (double)n) : 0.0;
+  const double c = mode ? scal[1] : 1.0;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long)gridDim.x * blockDim.x) {
+    const long lr = e / n, j = e % n;
+    const long i = ((lr >> 7) * nparts + part) * 128 + (lr & 127);
+    double v = 0.0;
+    if (i < n && j >= ((i >> 8) << 8)) {
+      v = (double)C32[lr * ld32 + j];
+      if (mode) {
+        v = __dadd_rn(v, __dmul_rn(alpha, m[i]));
+        v = __dadd_rn(v, __dmul_rn(alpha, m[j]));
+        v = __dadd_rn(v, shift);
+        if (do_scale) v = v / c;
+      }
+    }
+    out[e] = v;
+  }
+}
+
 // mode 0 fallback GEMM: dp4a SIMT, 64x64 output tile per block, upper-triangle blocks only.
 // C32[i][j] (+)= sum_k X8[i][k] X8[j][k]
 __global__ void __launch_bounds__(256)

@@ -29,7 +29,9 @@ constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barr
 constexpr int TC_THREADS = 192;
 
 struct TileCoord {
-  int mi, nj;
+  int mi, nj;  // operand tiles: rows mi*128.. of X against rows nj*256.. of X
+  int mo;      // output row tile: C32 row = mo*128 + r (== mi unless the output is a compact
+               // panel of one partition's row tiles, crossprod.cu)
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -67,37 +69,38 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const TileCoord tc = tiles[t];
-        for (int kb = 0; kb < num_kblocks; kb++) {
-          mbar_wait(&empty[stage], phase ^ 1);
+    // ===== TMA producer (whole warp walks the protocol, one elected lane issues) =====
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const TileCoord tc = tiles[t];
+      for (int kb = 0; kb < num_kblocks; kb++) {
+        mbar_wait_warp(&empty[stage], phase ^ 1);
+        if (elect_one()) {
           uint8_t *sa = smem + stage * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
           mbar_expect_tx(&full[stage], TC_STAGE_BYTES);
           tma_load_2d(sa, &tmap_a, &full[stage], kb * TC_BK, tc.mi * TC_BM);
           tma_load_2d(sb, &tmap_b, &full[stage], kb * TC_BK, tc.nj * TC_BN);
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_i8(TC_BM, TC_BN, 0, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1);
+    // ===== MMA issuer (elect.sync issue: no uniformisation loops around UTCIMMA) =====
+    constexpr uint32_t idesc = make_idesc_i8(TC_BM, TC_BN, 0, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      mbar_wait_warp(&tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * TC_BN;
+      for (int kb = 0; kb < num_kblocks; kb++) {
+        mbar_wait_warp(&full[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * TC_BN;
-        for (int kb = 0; kb < num_kblocks; kb++) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
+        if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * TC_STAGE_BYTES);
           const uint64_t adesc = make_desc_k_sw128(sa);
           const uint64_t bdesc = make_desc_k_sw128(sa + TC_A_BYTES);
@@ -105,11 +108,12 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int k4 = 0; k4 < TC_BK / 32; k4++)  // +32 bytes along K = +2 in the >>4 address field
             mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
           tc_commit(&empty[stage]);
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+          if (kb == num_kblocks - 1) tc_commit(&tfull[acc]);
         }
-        tc_commit(&tfull[acc]);
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        __syncwarp();
+        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
       }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
@@ -120,7 +124,7 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const TileCoord tc = tiles[t];
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      const long row = (long)tc.mi * TC_BM + quad * 32 + lane;
+      const long row = (long)tc.mo * TC_BM + quad * 32 + lane;
       int32_t *crow = C32 + row * ld32 + (long)tc.nj * TC_BN;
       const uint32_t taddr = tmem_base + acc * TC_BN + ((uint32_t)(quad * 32) << 16);
 #pragma unroll 1
@@ -192,15 +196,20 @@ int make_tmap_u8_2d(CUtensorMap *map, const void *base, long row_bytes, long row
 
 // Upper-triangle tile list in super-blocks of 16 x 8 tiles (2048 x 2048 outputs) so that the
 // ~148 tiles in flight share operand panels in L2.
-int build_tile_list(long rows, TileCoord **d_tiles, int *num_tiles, cudaStream_t stream) {
+// part/nparts: row tile mi belongs to partition mi % nparts and is written to the compact output
+// row tile mi / nparts (2-D output-tile partition over GPUs: no communication, cyclic = balanced).
+int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
+                    cudaStream_t stream) {
   const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
   std::vector<TileCoord> v;
   for (int sn = 0; sn < Nt; sn += 8)
-    for (int sm = 0; sm < Mt; sm += 16)
+    for (int sm = 0; sm < Mt; sm += 16 * nparts)
       for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
-        for (int mi = sm; mi < sm + 16 && mi < Mt; mi++)
-          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj});
-  *num_tiles = (int)v.size();
+        for (int mi = sm + part; mi < sm + 16 * nparts && mi < Mt; mi += nparts)
+          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts});
+  const int real_tiles = (int)v.size();
+  if (v.empty()) v.push_back({0, 0, 0});  // keep the allocation non-empty; the launch is skipped
+  *num_tiles = real_tiles;
   MB_CUDA(cudaMallocAsync(d_tiles, sizeof(TileCoord) * v.size(), stream));
   MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice,
                           stream));
@@ -217,6 +226,7 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
   CUtensorMap ta, tb;
   MB_CHECK(make_tmap_u8_2d(&ta, X8, kcols, rows_pad, pitch, TC_BK, TC_BM, 1));
   MB_CHECK(make_tmap_u8_2d(&tb, X8, kcols, rows_pad, pitch, TC_BK, TC_BN, 1));
+  if (num_tiles <= 0) return 0;
   const int grid = num_tiles < sm_count ? num_tiles : sm_count;
   crossprod_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
                                                              (int)(kcols / TC_BK), C32, ld32,

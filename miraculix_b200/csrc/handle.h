@@ -84,4 +84,9 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
                      const double *d_f, int do_scale, double *d_ans, cudaStream_t stream,
                      CrossprodTiming *timing);
 
+long crossprod_partition_rows(long rows, int part, int nparts);
+int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
+                               const double *d_f, int do_scale, int part, int nparts,
+                               double *d_panel, cudaStream_t stream, CrossprodTiming *timing);
+
 }  // namespace mb200

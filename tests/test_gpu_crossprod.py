@@ -145,3 +145,32 @@ def test_grm_properties_full_size(gpu_lib):
     finally:
         api.set_options(use_gpu=True, not_center=False)
         api.free_compressed(h)
+
+
+@pytest.mark.parametrize("snps,indiv,nparts", [(1003, 700, 3), (953, 1500, 8), (300, 100, 2)])
+def test_grm_partition_assembles_to_full(gpu_lib, snps, indiv, nparts):
+    """2-D output-tile partition: the panels of all partitions, mirrored, equal the
+    single-GPU result bit for bit -- raw counts and the centred/scaled GRM (whose row sums the
+    partitions obtain exactly from the input, without exchanging anything)."""
+    from miraculix_b200 import api
+    plink, Z, f = simulate.simulate(snps, indiv, seed=snps + nparts)
+    x = simulate.pack_2bit(Z)
+    for mode in (0, 1):
+        full = api.snp_crossprod(x, snps, indiv, is_snpmajor=False) if mode == 0 else \
+            api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
+        got = np.full((indiv, indiv), np.nan)
+        seen = 0
+        for part in range(nparts):
+            rows, panel = api.grm_partition(x, snps, indiv, part, nparts, mode=mode, do_scale=True,
+                                            allele_freq=f)
+            for lr, i in enumerate(rows):
+                if i >= indiv:
+                    assert not panel[lr].any()  # padding rows of the last tile
+                    continue
+                first = (i // 256) * 256
+                assert not panel[lr, :first].any()
+                got[i, first:] = panel[lr, first:]
+                seen += 1
+        assert seen == indiv  # every row owned exactly once
+        iu = np.triu_indices(indiv)
+        assert np.array_equal(got[iu], full[iu]), mode
