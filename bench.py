@@ -44,6 +44,10 @@ def parse_args():
     ap.add_argument("--ncol", type=int, default=10)
     ap.add_argument("--no-grm", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-pcg", action="store_true")
+    ap.add_argument("--pcg-snps", type=int, default=500_000)
+    ap.add_argument("--pcg-indiv", type=int, default=200_000)
+    ap.add_argument("--pcg-iters", type=int, default=20)
     ap.add_argument("--grm-snps", type=int, default=50_000)
     ap.add_argument("--grm-indiv", type=int, default=10_000)
     ap.add_argument("--cpu-snps", type=int, default=100_000)
@@ -280,6 +284,9 @@ def run_ours(args):
     if world == 1 and lib.mb200_last_status() != 0:
         raise SystemExit("dgemm_compressed failed: " + lib.mb200_last_message().decode())
     clocks = sampler.stop() if sampler else None
+    pcg = None
+    if not args.no_pcg:
+        pcg = run_pcg(args, lib, api, dev, rank, world)
 
     units_step = 2.0 * snps * indiv * ncol
     value = units_step * args.steps / (total_ms * 1e-3)
@@ -345,6 +352,8 @@ def run_ours(args):
                            "ShardedCompressed with pinned host B/C + NCCL all-reduce"},
             "gpu_launches": int(launches), "clocks": clocks}
 
+    if pcg is not None:
+        line["pcg"] = pcg
     if not args.no_grm and world == 1:
         line["grm"] = run_grm(args, lib, api, dev)
     if not args.no_cpu:
@@ -354,6 +363,69 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                                     "sample": f"failed: {exc}"}
     print(json.dumps(line))
+
+
+def run_pcg(args, lib, api, dev, rank, world):
+    """BASELINE configs[3]: conjugate gradients on (Zc Zc^T + lambda I) x = b, 500k SNPs x 200k
+    individuals, packed matrix resident and SNP-sharded over the ranks; one iteration = one 't' and
+    one 'n' product with a single column + ONE all-reduce of indiv doubles (mb200_cg_solve_device).
+    Every rank runs it (collective); rank 0 reports."""
+    import torch
+    import torch.distributed as dist
+    from miraculix_b200.sharded import ShardedCompressed
+    snps, indiv, iters = args.pcg_snps, args.pcg_indiv, args.pcg_iters
+    sh = ShardedCompressed(None, snps, indiv, rank, world)
+    s_loc, bs = sh.s_count, (indiv + 3) // 4
+    bed = torch.empty(s_loc * bs, dtype=torch.uint8, device=dev)
+    api._check(lib.mb200_simulate_plink_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, 3000 + rank),
+               "simulate")
+    h = C.c_void_p(None)
+    api._check(lib.mb200_plink2compressed_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, None, 1,
+                                                 C.byref(h)), "plink2compressed_device")
+    del bed
+    torch.cuda.empty_cache()
+    sh.handle = h
+    stream = sh.stream()
+    g = torch.Generator(device=dev)
+    g.manual_seed(11)
+    b = torch.randn(indiv, dtype=torch.float64, device=dev, generator=g)
+    x = torch.zeros(indiv, dtype=torch.float64, device=dev)
+    lam = 0.05 * snps
+    sh.cg_solve(b, x, lam=lam, tol=0.0, max_iter=2)  # warm-up (workspace, NCCL channel)
+    x.zero_()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = api.kernel_launches()
+    e0.record(stream)
+    it, res = sh.cg_solve(b, x, lam=lam, tol=0.0, max_iter=iters)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    launches = api.kernel_launches() - launches0
+    bnorm = float(b.norm().item())
+    sh._stream = None
+    del stream
+    lib.free_compressed(C.byref(h))
+    if rank != 0:
+        return None
+    hbm, _bf16, _src = peaks()
+    products = it + 1                                     # the initial G x0 and one per iteration
+    ms_iter = float(ms.item()) / products
+    alg_bytes = 2.0 * snps * bs + 8.0 * 2 * (snps + indiv)  # both orientations once + vectors
+    gbs = alg_bytes / world / (ms_iter * 1e-3) / 1e9
+    return {"workload": f"CG on (ZcZc^T + {lam:g} I) x = b, {snps} SNPs x {indiv} individuals "
+                        f"(BASELINE configs[3]), packed matrix resident, SNP-sharded over {world} GPU(s)",
+            "iterations": it, "ms_per_iteration": ms_iter,
+            "value": 2.0 * snps * indiv / (ms_iter * 1e-3), "unit": UNIT,
+            "residual_reduction": res / bnorm, "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU",
+                         "frac": gbs / hbm,
+                         "note": "algorithmic bytes = both packed orientations once per iteration "
+                                 "(ncol = 1: 't' then 'n'), per GPU"}}
 
 
 def run_grm(args, lib, api, dev):

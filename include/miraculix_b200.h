@@ -166,6 +166,27 @@ int mb200_grm_partition(unsigned char *snp_matrix, int snps, int indiv, bool is_
  * [0] expand+GEMM, [1] epilogue (int32 -> fp64, symmetrise, centre), [2] executed int8 ops. */
 int mb200_crossprod_last_timing(double out[3]);
 
+/* ------------------------------------------------------------------------------------------
+ * Device-resident conjugate gradients (BASELINE configs[3]).
+ * Replaces the host loop of examples/iterative_solver/grm_solve_cg.jl:109-133 (GRM_vec :75-85):
+ * solves (Zc Zc^T + lambda I) x = b, Zc = Z - 2 1 f^T (or raw Z with do_not_center), with the
+ * reference script's recurrences; x holds the start vector on entry and the iterate on return.
+ * Stops when ||r|| < tol (checked before every iteration, as :118-121) or after max_iter
+ * iterations; *iters = iterations done, *resid_norm = ||r||.  Packed matrix and vectors never
+ * leave the GPU; the host reads one scalar per iteration.
+ * SNP-sharded solves (one handle per GPU holding the SNP range S_g): pass an
+ * `allreduce` hook; it is called once per matrix-vector product with the rank's partial
+ * Z[:,S_g] Z[:,S_g]^T p (indiv doubles, device memory) and must sum it in place over all ranks,
+ * asynchronously on `stream` (e.g. ncclAllReduce / torch.distributed.all_reduce).  Return 0 on
+ * success.  NULL = single GPU. */
+typedef int (*mb200_allreduce_fn)(double *d_buf, long count, void *stream, void *user);
+int mb200_cg_solve_device(void *compressed, const double *d_b, double *d_x, double lambda,
+                          double tol, int max_iter, mb200_allreduce_fn allreduce, void *user,
+                          int *iters, double *resid_norm);
+/* Same with HOST vectors b, x of length indiv (single GPU). */
+int mb200_cg_solve(void *compressed, const double *b, double *x, double lambda, double tol,
+                   int max_iter, int *iters, double *resid_norm);
+
 #ifdef __cplusplus
 }
 #endif

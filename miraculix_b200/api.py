@@ -65,7 +65,14 @@ SIGNATURES = {
     "mb200_grm_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_bool, C.c_int, C.c_void_p,
                                       C.c_bool, C.c_int, C.c_int, C.c_void_p]),
     "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
+    "mb200_cg_solve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
+                                        C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int),
+                                        C.POINTER(C.c_double)]),
+    "mb200_cg_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int,
+                                 C.POINTER(C.c_int), C.POINTER(C.c_double)]),
 }
+# mb200_allreduce_fn: int (*)(double *d_buf, long count, void *stream, void *user)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p)
 
 
 def load_library(path: str | None = None):
@@ -243,6 +250,34 @@ def grm_partition(x: np.ndarray, snps: int, indiv: int, part: int, nparts: int, 
         _check(rc, "mb200_grm_partition")
     lr = np.arange(lrows)
     return ((lr // 128) * nparts + part) * 128 + lr % 128, panel
+
+
+def cg_solve(handle: C.c_void_p, b: np.ndarray, x0: np.ndarray, lam: float = 0.0,
+             tol: float = 1e-2, max_iter: int = 1000):
+    """The conjugate-gradient loop of examples/iterative_solver/grm_solve_cg.jl:109-133 run on the
+    device: solves (Zc Zc^T + lam I) x = b from the start vector x0 (host vectors of length
+    indiv).  Returns (x, iterations, ||r||)."""
+    b = np.ascontiguousarray(b, dtype=np.float64).ravel()
+    x = np.array(x0, dtype=np.float64, copy=True).ravel()
+    if b.shape != x.shape:
+        raise ValueError("b and x0 must have the same length (indiv)")
+    it, res = C.c_int(0), C.c_double(0.0)
+    rc = load_library().mb200_cg_solve(handle, b.ctypes.data, x.ctypes.data, lam, tol, max_iter,
+                                       C.byref(it), C.byref(res))
+    _check(rc, "mb200_cg_solve")
+    return x, it.value, res.value
+
+
+def cg_solve_device(handle: C.c_void_p, d_b: int, d_x: int, lam: float, tol: float, max_iter: int,
+                    allreduce=None):
+    """Device-pointer variant; `allreduce` is an ALLREDUCE_FN (or None) summing the rank's partial
+    matrix-vector product over the SNP shards (see include/miraculix_b200.h)."""
+    it, res = C.c_int(0), C.c_double(0.0)
+    cb = C.cast(allreduce, C.c_void_p) if allreduce is not None else None
+    rc = load_library().mb200_cg_solve_device(handle, C.c_void_p(d_b), C.c_void_p(d_x), lam, tol,
+                                              max_iter, cb, None, C.byref(it), C.byref(res))
+    _check(rc, "mb200_cg_solve_device")
+    return it.value, res.value
 
 
 def crossprod_last_timing():

@@ -122,6 +122,8 @@ static void destroy_handle(Handle *h) {
   cudaFree(h->d_C);
   cudaFree(h->d_w);
   cudaFree(h->d_Bq);
+  cudaFree(h->d_cg);
+  if (h->h_cg) cudaFreeHost(h->h_cg);
   if (h->pinned) cudaFreeHost(h->pinned);
   for (int i = 0; i < Handle::kEvRing; i++) {
     if (h->ev_begin[i]) cudaEventDestroy(h->ev_begin[i]);

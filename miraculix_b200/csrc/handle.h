@@ -49,6 +49,9 @@ struct Handle {
   double rowsum_max[2] = {0, 0};  // max_r sum_k z_rk of the indiv-major / snp-major layout
   int8_t *d_Bq = nullptr;  // sliced int8 panel for the tensor-core path
   size_t bq_bytes = 0;
+  void *d_cg = nullptr;    // conjugate-gradient workspace (solver.cu), allocated on first use
+  size_t cg_bytes = 0;
+  void *h_cg = nullptr;    // pinned scalars the solver's kernels write for the host
   void *pinned = nullptr;  // pinned staging for host<->device copies of B / C
   size_t pinned_bytes = 0;
   cudaStream_t stream = nullptr;

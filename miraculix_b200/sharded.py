@@ -98,3 +98,37 @@ class ShardedCompressed:
         if self.s_count > 0:
             self._local(1, B, C_local)
         return C_local
+
+    # -- conjugate gradients over the shards ------------------------------------------------
+    def cg_solve(self, b, x, lam: float = 0.0, tol: float = 1e-2, max_iter: int = 1000):
+        """(Zc Zc^T + lam I) x = b with the matrix SNP-sharded over the ranks (BASELINE
+        configs[3]; loop of examples/iterative_solver/grm_solve_cg.jl:109-133 inside the C-ABI
+        library, mb200_cg_solve_device).  b, x: replicated CUDA tensors of length indiv; x holds
+        the start vector and receives the iterate.  The only exchange is ONE all-reduce of indiv
+        doubles per matrix-vector product, issued from the library's hook on its own stream.
+        Returns (iterations, ||r||)."""
+        import torch
+        import torch.distributed as dist
+        from . import api
+
+        hook = None
+        if self.world > 1:
+            stream, group, dev = self.stream(), self.group, x.device
+
+            class _Dev:  # a device buffer of the library seen through __cuda_array_interface__
+                def __init__(self, ptr, n):
+                    self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8",
+                                                     "data": (ptr, False), "version": 2}
+
+            def _allreduce(ptr, count, _stream, _user):
+                try:
+                    t = torch.as_tensor(_Dev(ptr, count), device=dev)
+                    with torch.cuda.stream(stream):
+                        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+                    return 0
+                except Exception as exc:  # never unwind through the C frames
+                    print(f"sharded cg: all-reduce failed: {exc}")
+                    return 1
+
+            hook = api.ALLREDUCE_FN(_allreduce)
+        return api.cg_solve_device(self.handle, b.data_ptr(), x.data_ptr(), lam, tol, max_iter, hook)

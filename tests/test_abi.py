@@ -16,6 +16,7 @@ HEADER = os.path.join(ROOT, "include", "miraculix_b200.h")
 def declared_symbols():
     src = open(HEADER).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"typedef\s+[^;{]*\(\s*\*[^;]*;", "", src)  # function-pointer typedefs
     return sorted(set(re.findall(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\([^;{]*\)\s*;", src)))
 
 

@@ -127,3 +127,21 @@ def test_ld_epilogue_is_correlation():
     R = cport.ld_epilogue(M, indiv, f)
     want = np.corrcoef(Z.T.astype(np.float64))
     assert relerr(R, want) < 1e-10
+
+
+def test_oracle_cg_restatement_solves_the_dense_system():
+    """oracle/cg.py (the reference script's loop, grm_solve_cg.jl:109-133) against a dense numpy
+    solve of (Zc Zc^T + lam I) x = b, and against the live reference library as the product."""
+    from oracle import cg as ocg
+    snps, indiv = 700, 90
+    plink, Z, f = simulate.simulate(snps, indiv, seed=9, missing=0.01)
+    rng = np.random.default_rng(10)
+    b, x0 = rng.standard_normal(indiv), rng.standard_normal(indiv)
+    lam = 0.05 * snps
+    Zc = Z.astype(np.float64) - 2.0 * f[None, :]            # indiv x snps
+    G = Zc @ Zc.T + lam * np.eye(indiv)
+    x, it, res = ocg.cg_solve(plink, snps, indiv, f, b, x0, lam=lam, tol=1e-9, max_iter=400)
+    assert it < 400 and res < 1e-9
+    assert np.abs(x - np.linalg.solve(G, b)).max() <= 1e-9 * np.abs(x).max()
+    v = rng.standard_normal(indiv)
+    assert np.abs(ocg.grm_vec(plink, snps, indiv, f, v) - Zc @ (Zc.T @ v)).max() <= 1e-9 * snps
