@@ -287,6 +287,9 @@ def run_ours(args):
     pcg = None
     if not args.no_pcg:
         pcg = run_pcg(args, lib, api, dev, rank, world)
+    grm_part = None
+    if not args.no_grm and world > 1:
+        grm_part = run_grm_partition(args, lib, api, dev, rank, world)
 
     units_step = 2.0 * snps * indiv * ncol
     value = units_step * args.steps / (total_ms * 1e-3)
@@ -356,6 +359,8 @@ def run_ours(args):
         line["pcg"] = pcg
     if not args.no_grm and world == 1:
         line["grm"] = run_grm(args, lib, api, dev)
+    if grm_part is not None:
+        line["grm"] = grm_part
     if not args.no_cpu:
         try:
             line["cpu_baseline"] = run_cpu_baseline(args)
@@ -426,6 +431,63 @@ def run_pcg(args, lib, api, dev, rank, world):
                          "frac": gbs / hbm,
                          "note": "algorithmic bytes = both packed orientations once per iteration "
                                  "(ncol = 1: 't' then 'n'), per GPU"}}
+
+
+def run_grm_partition(args, lib, api, dev, rank, world):
+    """configs[1]/[4] over N GPUs: 2-D output-tile partition, NO communication -- every rank holds
+    the packed matrix and computes the 128-row tiles t with t % N == rank of the centred GRM
+    (mb200_crossprod_partition_device).  Time = max over ranks of the device time."""
+    import torch
+    import torch.distributed as dist
+    snps, indiv = args.grm_snps, args.grm_indiv
+    bs = (indiv + 3) // 4
+    bed = torch.empty(snps * bs, dtype=torch.uint8, device=dev)
+    api._check(lib.mb200_simulate_plink_device(C.c_void_p(bed.data_ptr()), snps, indiv, 4242), "simulate")
+    h = C.c_void_p(None)
+    api._check(lib.mb200_plink2compressed_device(C.c_void_p(bed.data_ptr()), snps, indiv, None, 1,
+                                                 C.byref(h)), "plink2compressed_device")
+    del bed
+    lay = api.get_layout(h)
+    kcols = lay.pitch_indiv_major * 4
+    f = torch.zeros(kcols, dtype=torch.float64, device=dev)
+    f[:snps].copy_(torch.frombuffer(bytearray(api.get_compressed_freq(h, snps).tobytes()),
+                                    dtype=torch.float64))
+    lrows = lib.mb200_crossprod_partition_rows(indiv, rank, world)
+    panel = torch.empty(max(1, lrows) * indiv, dtype=torch.float64, device=dev)
+    gemm, epi, ops = [], [], 0.0
+    reps = args.warmup + max(3, min(args.steps, 10))
+    for it in range(reps):
+        dist.barrier()
+        api._check(lib.mb200_crossprod_partition_device(C.c_void_p(lay.d_indiv_major), kcols, indiv, 0, 1,
+                                                        C.c_void_p(f.data_ptr()), 1, rank, world,
+                                                        C.c_void_p(panel.data_ptr())), "crossprod_partition")
+        t = api.crossprod_last_timing()
+        if it >= args.warmup:
+            gemm.append(t["gemm_ms"])
+            epi.append(t["epilogue_ms"])
+            ops = t["executed_ops"]
+    torch.cuda.synchronize()
+    lib.free_compressed(C.byref(h))
+    v = torch.tensor([statistics.mean(gemm), statistics.mean(epi), ops], dtype=torch.float64, device=dev)
+    vmax = v.clone()
+    dist.all_reduce(vmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(v, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        return None
+    gm, ep, ops_sum = float(vmax[0]), float(vmax[1]), float(v[2])
+    tot = gm + ep
+    alg_ops = 2.0 * indiv * indiv * snps
+    int8_peak = 4500.0
+    return {"workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals (BASELINE configs[1]), "
+                        f"2-D output-tile partition over {world} GPUs, no communication",
+            "metric": "GRM crossproduct int8 TOPS", "value": alg_ops / (tot * 1e-3) / 1e12,
+            "unit": "TOPS (2*indiv^2*snps / t, full-matrix count)", "ms": tot,
+            "expand_gemm_ms": gm, "epilogue_ms": ep,
+            "roofline": {"bound": "tensor", "achieved": ops_sum / (gm * 1e-3) / 1e12 / world,
+                         "peak": int8_peak, "unit": "TOP/s per GPU",
+                         "frac": ops_sum / (gm * 1e-3) / 1e12 / world / int8_peak, "traffic": None,
+                         "peak_source": "nominal int8 dense",
+                         "note": "achieved = EXECUTED ops of all ranks / (max expand+GEMM time x N)"}}
 
 
 def run_grm(args, lib, api, dev):

@@ -86,6 +86,11 @@ unsigned long long mb200_kernel_launches(void);
  *   rowsum_max * 2^(e_c - 47) <= 5e-11 * max_r |C[r,c]|   for every column c
  * and recomputed with 8 digits (error <= 2^-62 relative to max|B_c|) when the bound fails. */
 int mb200_set_dgemm_mode(int mode, int slices);
+/* Host-pointer dgemm_compressed overlaps the PCIe copies of the snps x n panel (B for 'N', C for
+ * 'T') with the kernels by cutting the SNP axis into `chunks` pieces (default 4, at most 16;
+ * boundaries multiples of 512 SNPs) whenever that panel holds at least min_bytes (default 4e6;
+ * negative = keep).  Results do not depend on the chunking beyond fp64 summation order. */
+int mb200_set_pipeline(int chunks, double min_bytes);
 /* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct (default). */
 int mb200_set_crossprod_mode(int mode);
 

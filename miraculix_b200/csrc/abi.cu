@@ -49,6 +49,8 @@ Options &options() {
     if (const char *e = getenv("MB200_DGEMM_MODE")) o.dgemm_mode = atoi(e);
     if (const char *e = getenv("MB200_DGEMM_SLICES")) o.dgemm_slices = atoi(e);
     if (const char *e = getenv("MB200_CROSSPROD_MODE")) o.crossprod_mode = atoi(e);
+    if (const char *e = getenv("MB200_PIPE_CHUNKS")) o.pipe_chunks = atoi(e);
+    if (const char *e = getenv("MB200_PIPE_MIN_BYTES")) o.pipe_min_bytes = atof(e);
   }
   return o;
 }
@@ -124,6 +126,10 @@ static void destroy_handle(Handle *h) {
   cudaFree(h->d_Bq);
   cudaFree(h->d_cg);
   if (h->h_cg) cudaFreeHost(h->h_cg);
+  if (h->h_pipe) cudaFreeHost(h->h_pipe);
+  if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+  for (int i = 0; i < Handle::kPipeMax; i++)
+    if (h->ev_pipe[i]) cudaEventDestroy(h->ev_pipe[i]);
   if (h->pinned) cudaFreeHost(h->pinned);
   for (int i = 0; i < Handle::kEvRing; i++) {
     if (h->ev_begin[i]) cudaEventDestroy(h->ev_begin[i]);
@@ -161,6 +167,10 @@ static int create_handle(long snps, long indiv, int max_n, Handle **out) {
     }                                                                                 \
   } while (0)
   H_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  H_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < Handle::kPipeMax; i++)
+    H_CUDA(cudaEventCreateWithFlags(&h->ev_pipe[i], cudaEventDisableTiming));
+  H_CUDA(cudaMallocHost(&h->h_pipe, 64));
   for (int i = 0; i < Handle::kEvRing; i++) {
     H_CUDA(cudaEventCreate(&h->ev_begin[i]));
     H_CUDA(cudaEventCreate(&h->ev_end[i]));
@@ -227,6 +237,12 @@ int mb200_set_dgemm_mode(int mode, int slices) {
   Options &o = options();
   if (mode == 0 || mode == 1) o.dgemm_mode = mode;
   if (slices == 0 || (slices >= 3 && slices <= 8)) o.dgemm_slices = slices;
+  return 0;
+}
+int mb200_set_pipeline(int chunks, double min_bytes) {
+  Options &o = options();
+  if (chunks >= 1) o.pipe_chunks = chunks > Handle::kPipeMax ? Handle::kPipeMax : chunks;
+  if (min_bytes >= 0) o.pipe_min_bytes = min_bytes;
   return 0;
 }
 int mb200_set_crossprod_mode(int mode) {
@@ -388,6 +404,8 @@ static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, do
     return fail(-2, __func__, __LINE__, "leading dimension too small: ldb=%ld (need %ld) ldc=%ld (need %ld)",
                 ldb, k, ldc, m);
   if (n <= 0) return 0;
+  if (options().dgemm_mode == 1)  // tensor-core path: PCIe copies pipelined against the kernels
+    return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc);
   if (ldb == k)
     MB_CUDA(cudaMemcpyAsync(h->d_B, B, sizeof(double) * k * n, cudaMemcpyHostToDevice, h->stream));
   else

@@ -41,30 +41,64 @@ center_w_kernel(const double *__restrict__ B, long ldb, long k, const double *__
 }
 __global__ void __launch_bounds__(256)
 init_c_kernel(double *__restrict__ C, long ldc, long m, int n, const double *__restrict__ w,
-              const double *__restrict__ y, int centered, const int *__restrict__ guard) {
+              const double *__restrict__ y, int centered, int accumulate,
+              const int *__restrict__ guard) {
   if (guard && *guard == 0) return;
   const long r = (long)blockIdx.x * 256 + threadIdx.x;
   if (r >= m) return;
   const double yr = y ? y[r] : 1.0;
-  for (int c = 0; c < n; c++) C[r + (size_t)c * ldc] = centered ? w[c] * yr : 0.0;
+  for (int c = 0; c < n; c++) {
+    const double v = centered ? w[c] * yr : 0.0;
+    double *dst = &C[r + (size_t)c * ldc];
+    *dst = accumulate ? *dst + v : v;
+  }
 }
 
-int dgemm_center_init(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
+DgemmView full_view(const Handle *h, int trans) {
+  DgemmView v;
+  v.trans = trans;
+  v.Z = trans ? h->d_snp_major : h->d_indiv_major;
+  v.pitch = trans ? h->pitch_s : h->pitch_i;
+  v.rows = trans ? h->snps : h->indiv;
+  v.K = trans ? h->indiv : h->snps;
+  v.x = trans ? nullptr : h->d_f;
+  v.y = trans ? h->d_f : nullptr;
+  v.rowsum_max = h->rowsum_max[trans ? 1 : 0];
+  return v;
+}
+// SNP range [begin, begin + count): for 'N' a K range (begin must be a multiple of 512 SNPs =
+// 128 packed bytes), for 'T' a row range.  The full-row bound on the row sums stays valid.
+DgemmView sub_view(const Handle *h, int trans, long begin, long count) {
+  DgemmView v = full_view(h, trans);
+  if (trans) {
+    v.Z += begin * v.pitch;
+    v.rows = count;
+    v.y = h->d_f + begin;
+  } else {
+    v.Z += begin / 4;
+    v.K = count;
+    v.x = h->d_f + begin;
+  }
+  return v;
+}
+
+// C (+)= -2 (x^T B) y^T, the centring term of the view (reference dgemm_compressed_cuda.cu:421-459)
+int dgemm_center_init(Handle *h, const DgemmView &v, int n, const double *dB, long ldb, double *dC,
                       long ldc, int centered, double *w, const int *guard) {
-  const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
   if (centered) {
     MB_CUDA(cudaMemsetAsync(w, 0, sizeof(double) * n, h->stream));
-    int ysplit = (int)(ceil_div(k, 256 * 16) < 64 ? ceil_div(k, 256 * 16) : 64);
+    int ysplit = (int)(ceil_div(v.K, 256 * 16) < 64 ? ceil_div(v.K, 256 * 16) : 64);
     if (ysplit < 1) ysplit = 1;
-    center_w_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dB, ldb, k, trans ? nullptr : h->d_f,
-                                                             w, guard);
+    center_w_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dB, ldb, v.K, v.x, w, guard);
     count_launch();
     MB_LAUNCH_CHECK();
   }
-  init_c_kernel<<<(unsigned)ceil_div(m, 256), 256, 0, h->stream>>>(
-      dC, ldc, m, n, w, trans ? h->d_f : nullptr, centered, guard);
-  count_launch();
-  MB_LAUNCH_CHECK();
+  if (centered || !v.accumulate) {
+    init_c_kernel<<<(unsigned)ceil_div(v.rows, 256), 256, 0, h->stream>>>(
+        dC, ldc, v.rows, n, w, v.y, centered, v.accumulate, guard);
+    count_launch();
+    MB_LAUNCH_CHECK();
+  }
   return 0;
 }
 
@@ -185,7 +219,7 @@ int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double
   const Options &o = options();
   if (o.dgemm_mode == 1 && dgemm_tc_available())
     return dgemm_tc_device(h, trans, n, dB, ldb, dC, ldc);
-  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered, h->d_w, nullptr));
+  MB_CHECK(dgemm_center_init(h, full_view(h, trans), n, dB, ldb, dC, ldc, o.centered, h->d_w, nullptr));
   const int ev = (int)(h->ev_count % Handle::kEvRing);
   h->ev_trans[ev] = trans;
   MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));

@@ -30,7 +30,7 @@ namespace mb200 {
 
 int make_tmap_u8_2d(CUtensorMap *map, const void *base, long row_bytes, long rows, long pitch,
                     int box_bytes, int box_rows, int swizzle128);
-int dgemm_center_init(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
+int dgemm_center_init(Handle *h, const DgemmView &v, int n, const double *dB, long ldb, double *dC,
                       long ldc, int centered, double *w, const int *guard);
 
 bool dgemm_tc_available() { return true; }
@@ -429,20 +429,31 @@ static int ensure_bq(Handle *h) {
 }
 
 // A-posteriori check of the digit count: the quantisation error of column c is at most
-// rowsum_max * 2^(e_c - P - 1) in every row; it must stay below tol * max_r |C[r,c]|.
+// rowsum_max * 2^(e_c - P - 1) in every row (e_c from the column maximum of B over ALL K ranges of
+// the call: the bounds of the ranges add up to at most that); it must stay below
+// tol * max_r |C[r,c]|.  The flag is sticky (row chunks of a 'T' call OR into it).
 __global__ void decide_kernel(const unsigned long long *__restrict__ amaxB,
-                              const int *__restrict__ exps,
                               const unsigned long long *__restrict__ amaxC, int n, int P,
                               double rowsum_max, double tol, int *__restrict__ flag) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= n || amaxB[c] == 0ull) return;  // zero column of B: exact
-  const double err = scalbn(rowsum_max, exps[c] - P - 1);
+  int e = 0;
+  frexp(__longlong_as_double((long long)amaxB[c]), &e);  // same exponent rule as quantize_kernel
+  const double err = scalbn(rowsum_max, e - P - 1);
   const double mc = __longlong_as_double((long long)amaxC[c]);
   if (!(err <= tol * mc)) atomicOr(flag, 1);
 }
+// amax_all[c] = max(amax_all[c], amax[c]) over the K ranges of one call
+__global__ void amax_merge_kernel(const unsigned long long *__restrict__ amax,
+                                  unsigned long long *__restrict__ amax_all, int n,
+                                  const int *__restrict__ guard) {
+  if (guard && *guard == 0) return;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < n && amax[c] > amax_all[c]) amax_all[c] = amax[c];
+}
 
-// Scratch inside d_w (8 M doubles, M = max_n + 16), one set per pass so that the guarded
-// fallback pass never races with the first one.
+// Scratch inside d_w (8 M doubles, M = max_n + 16).  Set 0 serves first passes, set 1 the guarded
+// fallback pass, so that the two never race; the tail holds what a whole call accumulates.
 struct TcScratch {
   double *w;
   unsigned long long *amaxB;
@@ -453,20 +464,51 @@ static TcScratch tc_scratch(Handle *h, int set) {
   double *base = h->d_w + (set ? 4 * M : 0);
   return {base, reinterpret_cast<unsigned long long *>(base + M), reinterpret_cast<int *>(base + 2 * M)};
 }
+static unsigned long long *tc_amaxC(Handle *h) {
+  return reinterpret_cast<unsigned long long *>(h->d_w + 3 * (h->max_n + 16));
+}
+static unsigned long long *tc_amax_all(Handle *h) {  // column maxima of B over the whole call
+  return reinterpret_cast<unsigned long long *>(h->d_w + 7 * (h->max_n + 16));
+}
+static int *tc_flag(Handle *h) { return reinterpret_cast<int *>(h->d_w + 8 * (h->max_n + 16) - 1); }
 
-// One full product at S digits per column: centre-init of C, then per column group
+struct TcEnv {
+  bool trace = false;
+  double tol = 5e-11;
+  int flags = 0, dbg = 0;
+};
+static const TcEnv &tc_env() {
+  static TcEnv env;
+  static bool init = false;
+  if (!init) {
+    init = true;
+    cudaFuncSetAttribute(dgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         dt_smem_bytes(DT_NMAX));
+    cudaFuncSetAttribute(dgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         dt_smem_bytes(DT_NMAX));
+    if (const char *e = getenv("MB200_TRACE")) env.trace = atoi(e) > 0;
+    if (const char *e = getenv("MB200_DGEMM_TOL")) env.tol = atof(e) > 0 ? atof(e) : env.tol;
+    if (const char *e = getenv("MB200_TC_FLAGS")) env.flags = atoi(e);
+    if (const char *e = getenv("MB200_DBG")) env.dbg = atoi(e);
+  }
+  return env;
+}
+
+// One product on a view at S digits per column: centring term into C, then per column group
 // colmax -> quantize -> main kernel.  guard != nullptr: every kernel is a no-op unless *guard.
-static int tc_pass(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc,
-                   int S, int set, const int *guard, bool trace, bool *first_main, int ev) {
+// amax_all (optional): receives the column maxima of B (merged over the K ranges of a call).
+static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long ldb, double *dC,
+                   long ldc, int S, int set, const int *guard, unsigned long long *amax_all,
+                   bool *first_main, int ev) {
   const Options &o = options();
-  const uint8_t *Z = trans ? h->d_snp_major : h->d_indiv_major;
-  const long pitch = trans ? h->pitch_s : h->pitch_i;
-  const long rows = trans ? h->snps : h->indiv, K = trans ? h->indiv : h->snps;
-  const long kpitch = pitch * 4;
+  const TcEnv &env = tc_env();
+  const long rows = v.rows, K = v.K;
+  const long row_bytes = round_up(ceil_div(K, 4), 128);  // the view's packed bytes per row
+  const long kpitch = (h->pitch_s > h->pitch_i ? h->pitch_s : h->pitch_i) * 4;
   const TcScratch sc = tc_scratch(h, set);
-  MB_CHECK(dgemm_center_init(h, trans, n, dB, ldb, dC, ldc, o.centered, sc.w, guard));
+  MB_CHECK(dgemm_center_init(h, v, n, dB, ldb, dC, ldc, o.centered, sc.w, guard));
   CUtensorMap tz;
-  MB_CHECK(make_tmap_u8_2d(&tz, Z, pitch, rows, pitch, 128, 128, 1));
+  MB_CHECK(make_tmap_u8_2d(&tz, v.Z, row_bytes, rows, v.pitch, 128, 128, 1));
   MB_CUDA(cudaMemsetAsync(sc.amaxB, 0, sizeof(unsigned long long) * n, h->stream));
 
   const int cpp = DT_NMAX / S;  // columns per pass
@@ -484,10 +526,10 @@ static int tc_pass(Handle *h, int trans, int n, const double *dB, long ldb, doub
     MB_LAUNCH_CHECK();
 
     CUtensorMap tb;
-    MB_CHECK(make_tmap_u8_2d(&tb, h->d_Bq, kpitch, N, kpitch, 128, N, 1));
+    MB_CHECK(make_tmap_u8_2d(&tb, h->d_Bq, row_bytes * 4, N, kpitch, 128, N, 1));
     DtParams p;
     p.rows = rows;
-    p.nchunks = (int)(pitch / 128);
+    p.nchunks = (int)(row_bytes / 128);
     p.R = dt_groups(N);
     p.row_blocks = (int)ceil_div(rows, p.R * 128);
     long ksplits = ceil_div(20L * h->sm_count, p.row_blocks);
@@ -503,74 +545,152 @@ static int tc_pass(Handle *h, int trans, int n, const double *dB, long ldb, doub
     p.ldc = ldc;
     p.exps = sc.exps + c0;
     p.guard = guard;
-    p.dbg = 0;
-    { static int fl = -1; if (fl < 0) { const char *e = getenv("MB200_TC_FLAGS"); fl = e ? atoi(e) : 0; } p.flags = fl; }
-    if (trace) { const char *e = getenv("MB200_DBG"); p.dbg = e ? atoi(e) : 0; }
+    p.flags = env.flags;
+    p.dbg = env.trace ? env.dbg : 0;
     const long units = (long)p.row_blocks * p.ksplits;
     const int grid = (int)(units < h->sm_count ? units : h->sm_count);
     if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
     *first_main = false;
-    if (trace) dgemm_tc_kernel<true><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+    if (env.trace) dgemm_tc_kernel<true><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
     else dgemm_tc_kernel<false><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+    count_launch();
+    MB_LAUNCH_CHECK();
+  }
+  if (amax_all) {
+    amax_merge_kernel<<<(unsigned)ceil_div(n, 64), 64, 0, h->stream>>>(sc.amaxB, amax_all, n, guard);
     count_launch();
     MB_LAUNCH_CHECK();
   }
   return 0;
 }
 
-int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc) {
-  const Options &o = options();
-  MB_CHECK(ensure_bq(h));
-  static bool attr_set = false;
-  static bool trace = false;
-  static double tol = 5e-11;
-  if (!attr_set) {
-    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 dt_smem_bytes(DT_NMAX)));
-    MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 dt_smem_bytes(DT_NMAX)));
-    const char *e = getenv("MB200_TRACE");
-    trace = e && atoi(e) > 0;
-    if (const char *t = getenv("MB200_DGEMM_TOL")) tol = atof(t) > 0 ? atof(t) : tol;
-    attr_set = true;
-  }
-  const long rows = trans ? h->snps : h->indiv, K = trans ? h->indiv : h->snps;
-  const int ev = (int)(h->ev_count % Handle::kEvRing);
-  h->ev_trans[ev] = trans;
-  bool first_main = true;
-
-  // Digit count.  Fixed (3..8) when asked for; otherwise adaptive: 8 digits where they cost
-  // nothing (n <= 2 fills one 16-row MMA either way; small problems), else 6 digits, verified
-  // against a rigorous bound and redone with 8 digits by guarded kernels if the bound fails.
-  int S = o.dgemm_slices;
-  bool adaptive = false;
+// Digit count.  Fixed (3..8) when asked for; otherwise adaptive: 8 digits where they cost
+// nothing (n <= 2 fills one 16-row MMA either way; small problems), else 6 digits, verified
+// against a rigorous bound and redone with 8 digits if the bound fails.
+static int tc_digits(int n, long rows, long K, bool *adaptive) {
+  int S = options().dgemm_slices;
+  *adaptive = false;
   if (S == 0) {
     if (n <= 2 || (double)rows * (double)K < 268435456.0) S = 8;
-    else { S = 6; adaptive = true; }
+    else { S = 6; *adaptive = true; }
   }
-  if (S < 3) S = 3;
-  if (S > 8) S = 8;
+  return S < 3 ? 3 : S > 8 ? 8 : S;
+}
+
+// colmax of C rows [0, rows) and the bound check; ORs into the call's flag
+static int tc_check(Handle *h, const double *dC, long ldc, long rows, int n, int S,
+                    const unsigned long long *amaxB, double rowsum_max) {
+  unsigned long long *amaxC = tc_amaxC(h);
+  MB_CUDA(cudaMemsetAsync(amaxC, 0, sizeof(unsigned long long) * n, h->stream));
+  int ysplit = (int)ceil_div(rows, 256 * 32);
+  if (ysplit > 128) ysplit = 128;
+  if (ysplit < 1) ysplit = 1;
+  colmax_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dC, ldc, rows, amaxC, nullptr);
+  decide_kernel<<<(unsigned)ceil_div(n, 64), 64, 0, h->stream>>>(amaxB, amaxC, n, 8 * S - 2,
+                                                                 rowsum_max, tc_env().tol, tc_flag(h));
+  count_launch(2);
+  MB_LAUNCH_CHECK();
+  return 0;
+}
+
+int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc) {
+  MB_CHECK(ensure_bq(h));
+  const DgemmView v = full_view(h, trans);
+  const int ev = (int)(h->ev_count % Handle::kEvRing);
+  h->ev_trans[ev] = trans;
+  bool first_main = true, adaptive = false;
+  const int S = tc_digits(n, v.rows, v.K, &adaptive);
   h->last_slices = S;
   h->last_adaptive = adaptive;
-  int *d_flag = reinterpret_cast<int *>(h->d_w + 8 * (h->max_n + 16) - 1);
-  MB_CHECK(tc_pass(h, trans, n, dB, ldb, dC, ldc, S, 0, nullptr, trace, &first_main, ev));
-  if (adaptive) {
-    const TcScratch sc = tc_scratch(h, 0);
-    unsigned long long *amaxC = reinterpret_cast<unsigned long long *>(h->d_w + 3 * (h->max_n + 16));
-    MB_CUDA(cudaMemsetAsync(amaxC, 0, sizeof(unsigned long long) * n, h->stream));
-    MB_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(int), h->stream));
-    int ysplit = (int)ceil_div(rows, 256 * 32);
-    if (ysplit > 128) ysplit = 128;
-    if (ysplit < 1) ysplit = 1;
-    colmax_kernel<<<dim3(n, ysplit), 256, 0, h->stream>>>(dC, ldc, rows, amaxC, nullptr);
-    decide_kernel<<<(unsigned)ceil_div(n, 64), 64, 0, h->stream>>>(
-        sc.amaxB, sc.exps, amaxC, n, 8 * S - 2, h->rowsum_max[trans ? 1 : 0], tol, d_flag);
-    count_launch(2);
-    MB_LAUNCH_CHECK();
-    MB_CHECK(tc_pass(h, trans, n, dB, ldb, dC, ldc, 8, 1, d_flag, trace, &first_main, ev));
+  MB_CHECK(tc_pass(h, v, n, dB, ldb, dC, ldc, S, 0, nullptr, nullptr, &first_main, ev));
+  if (adaptive) {  // no host sync: the 8-digit pass is launched guarded by the device flag
+    MB_CUDA(cudaMemsetAsync(tc_flag(h), 0, sizeof(int), h->stream));
+    MB_CHECK(tc_check(h, dC, ldc, v.rows, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
+    MB_CHECK(tc_pass(h, v, n, dB, ldb, dC, ldc, 8, 1, tc_flag(h), nullptr, &first_main, ev));
   }
   MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
   h->ev_count++;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host panels (the reference-facing dgemm_compressed): the PCIe copies are pipelined against the
+// kernels in SNP chunks (boundaries multiples of 512 SNPs).
+//   'N'  B has snps rows: chunk i of B is uploaded on the copy stream while the main kernel works
+//        on chunk i-1's SNP range (a K range of the individual-major layout, accumulating into C);
+//   'T'  C has snps rows: chunk i of C is downloaded while the kernel computes chunk i+1's rows.
+// The adaptive digit check ORs into one flag that travels back with the result; a failed check
+// (rare) redoes the whole product with 8 digits, unchunked.
+// ---------------------------------------------------------------------------------------------
+int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
+                            long ldc) {
+  MB_CHECK(ensure_bq(h));
+  const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
+  const DgemmView full = full_view(h, trans);
+  bool adaptive = false, first_main = true;
+  const int S = tc_digits(n, full.rows, full.K, &adaptive);
+  const int ev = (int)(h->ev_count % Handle::kEvRing);
+  h->ev_trans[ev] = trans;
+  h->last_slices = S;
+  h->last_adaptive = adaptive;
+
+  // chunks of the SNP axis: only worth it when the big panel takes a while on PCIe
+  int chunks = options().pipe_chunks;
+  if (chunks > Handle::kPipeMax) chunks = Handle::kPipeMax;
+  if (chunks < 1 || (double)h->snps * n * 8.0 < options().pipe_min_bytes) chunks = 1;
+  long per = round_up(ceil_div(h->snps, chunks), 512);
+  chunks = (int)ceil_div(h->snps, per);
+  int *h_flag = reinterpret_cast<int *>(h->h_pipe);
+  *h_flag = 0;
+  MB_CUDA(cudaMemsetAsync(tc_flag(h), 0, sizeof(int), h->stream));
+  auto copy2d = [](void *dst, long dld, const void *src, long sld, long rows, int cols,
+                   cudaMemcpyKind kind, cudaStream_t st) {
+    if (dld == rows && sld == rows)
+      return cudaMemcpyAsync(dst, src, sizeof(double) * rows * cols, kind, st);
+    return cudaMemcpy2DAsync(dst, sizeof(double) * dld, src, sizeof(double) * sld,
+                             sizeof(double) * rows, cols, kind, st);
+  };
+
+  if (!trans) {
+    MB_CUDA(cudaMemsetAsync(tc_amax_all(h), 0, sizeof(unsigned long long) * n, h->stream));
+    for (int i = 0; i < chunks; i++) {
+      const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
+      MB_CUDA(copy2d(h->d_B + s0, k, B + s0, ldb, cnt, n, cudaMemcpyHostToDevice, h->copy_stream));
+      MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
+      MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
+      DgemmView v = sub_view(h, 0, s0, cnt);
+      v.accumulate = i > 0;
+      MB_CHECK(tc_pass(h, v, n, h->d_B + s0, k, h->d_C, m, S, 0, nullptr, tc_amax_all(h),
+                       &first_main, ev));
+    }
+    if (adaptive) MB_CHECK(tc_check(h, h->d_C, m, m, n, S, tc_amax_all(h), full.rowsum_max));
+    MB_CUDA(copy2d(C, ldc, h->d_C, m, m, n, cudaMemcpyDeviceToHost, h->stream));
+  } else {
+    MB_CUDA(copy2d(h->d_B, k, B, ldb, k, n, cudaMemcpyHostToDevice, h->stream));
+    for (int i = 0; i < chunks; i++) {
+      const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
+      const DgemmView v = sub_view(h, 1, s0, cnt);
+      MB_CHECK(tc_pass(h, v, n, h->d_B, k, h->d_C + s0, m, S, 0, nullptr, nullptr, &first_main, ev));
+      if (adaptive)
+        MB_CHECK(tc_check(h, h->d_C + s0, m, cnt, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
+      MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->stream));
+      MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
+      MB_CUDA(copy2d(C + s0, ldc, h->d_C + s0, m, cnt, n, cudaMemcpyDeviceToHost, h->copy_stream));
+    }
+  }
+  if (adaptive)
+    MB_CUDA(cudaMemcpyAsync(h_flag, tc_flag(h), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
+  h->ev_count++;
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  MB_CUDA(cudaStreamSynchronize(h->copy_stream));
+  if (adaptive && *h_flag) {  // bound failed somewhere: exact-to-2^-62 redo, everything resident
+    first_main = false;
+    MB_CHECK(tc_pass(h, full, n, h->d_B, k, h->d_C, m, 8, 1, nullptr, nullptr, &first_main, ev));
+    MB_CUDA(copy2d(C, ldc, h->d_C, m, m, n, cudaMemcpyDeviceToHost, h->stream));
+    MB_CUDA(cudaStreamSynchronize(h->stream));
+    h->last_slices = 8;
+  }
   return 0;
 }
 
@@ -579,7 +699,7 @@ int dgemm_tc_last_precision(Handle *h, int *slices) {
   if (slices) *slices = h->last_slices;
   if (!h->last_adaptive) return 0;
   int flag = 0;
-  int *d_flag = reinterpret_cast<int *>(h->d_w + 8 * (h->max_n + 16) - 1);
+  int *d_flag = tc_flag(h);
   if (cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
       cudaStreamSynchronize(h->stream) != cudaSuccess)
     return -1;

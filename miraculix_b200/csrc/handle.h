@@ -17,6 +17,8 @@ struct Options {
   int dgemm_mode = 1;      // 0 fp64 SIMT, 1 int8-slice tcgen05
   int dgemm_slices = 0;    // 8-bit digits per column of B in mode 1; 0 = adaptive (6, verified, else 8)
   int crossprod_mode = 1;  // 0 dp4a SIMT, 1 tcgen05
+  int pipe_chunks = 4;             // SNP chunks of the host-pointer dgemm_compressed pipeline
+  double pipe_min_bytes = 4.0e6;   // ... used when the snps x n panel is at least this large
 };
 Options &options();
 
@@ -55,6 +57,11 @@ struct Handle {
   void *pinned = nullptr;  // pinned staging for host<->device copies of B / C
   size_t pinned_bytes = 0;
   cudaStream_t stream = nullptr;
+  // host-pointer dgemm_compressed pipelines the PCIe copies of B / C against the kernels:
+  cudaStream_t copy_stream = nullptr;
+  static constexpr int kPipeMax = 16;
+  cudaEvent_t ev_pipe[kPipeMax] = {nullptr};
+  void *h_pipe = nullptr;  // pinned word: the precision flag travels back with the result
   // ring of event pairs around the MAIN kernel of each dgemm_compressed call (bench.py reads
   // the per-launch durations of the timed region through mb200_dgemm_kernel_times)
   static constexpr int kEvRing = 128;
@@ -63,6 +70,20 @@ struct Handle {
   unsigned long long ev_count = 0;
   int sm_count = 148;
 };
+
+// A sub-problem of one orientation: rows x K genotypes starting at Z (row pitch `pitch` bytes).
+// 'N' views cut the SNP range (K) at multiples of 512 SNPs, 'T' views cut the SNP rows.
+struct DgemmView {
+  const uint8_t *Z = nullptr;
+  long pitch = 0, rows = 0, K = 0;
+  const double *x = nullptr;  // centring weights along K    (f for 'N', nullptr = ones for 'T')
+  const double *y = nullptr;  // centring weights along rows (f for 'T', nullptr = ones for 'N')
+  double rowsum_max = 0;      // upper bound of max_r sum_k z_rk over the view
+  int trans = 0;
+  int accumulate = 0;         // 1: C already holds earlier K ranges, add instead of initialise
+};
+DgemmView full_view(const Handle *h, int trans);
+DgemmView sub_view(const Handle *h, int trans, long begin, long count);  // SNP range [begin, begin+count)
 
 Handle *as_handle(void *p);  // validates magic, sets device; nullptr + status on failure
 
@@ -75,6 +96,9 @@ int rowsum_maxima(Handle *h);     // fills h->rowsum_max (synchronises the strea
 
 // dgemm.cu
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
+// Host panels B, C: copies pipelined against the kernels in SNP chunks (dgemm_tc.cu)
+int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
+                            long ldc);
 
 int dgemm_tc_read_trace(long long *out, int n);
 int dgemm_tc_last_precision(Handle *h, int *slices);  // dgemm_tc.cu, MB200_TRACE=1

@@ -213,3 +213,58 @@ def test_device_pointer_entry_and_simulator(gpu_lib):
         assert relerr(Cd.cpu().numpy().T, want) <= TOL
     finally:
         api.free_compressed(h)
+
+
+@pytest.mark.parametrize("chunks", [1, 2, 3, 5, 16])
+@pytest.mark.parametrize("snps,indiv,ncol", [(5000, 700, 10), (1537, 300, 3), (20000, 2500, 10)])
+def test_dgemm_host_pipeline_chunks(gpu_lib, snps, indiv, ncol, chunks):
+    """The host-pointer call cuts the SNP axis into chunks to overlap PCIe with the kernels
+    ('N': K ranges accumulate into C; 'T': row ranges): every chunking gives the oracle's result,
+    with leading dimensions, centred, missings, fixed and adaptive digits."""
+    from miraculix_b200 import api
+    plink, Z, f = simulate.simulate(snps, indiv, seed=snps + chunks, missing=0.01)
+    rng = np.random.default_rng(7)
+    gpu_lib.mb200_set_pipeline(chunks, 0.0)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    try:
+        for slices in (0, 7):
+            gpu_lib.mb200_set_dgemm_mode(1, slices)
+            for tr, k, m in (("N", snps, indiv), ("T", indiv, snps)):
+                ldb, ldc = k + 3, m + 8
+                Bbig = np.asfortranarray(rng.standard_normal((ldb, ncol)))
+                Cbig = np.full((ldc, ncol), 7.25, order="F")
+                gpu_lib.dgemm_compressed(tr.encode(), h, ncol, Bbig.ctypes.data, ldb,
+                                         Cbig.ctypes.data, ldc)
+                assert gpu_lib.mb200_last_status() == 0
+                want = cport.dgemm_compressed(tr, plink, snps, indiv, f, Bbig[:k], True)
+                assert relerr(Cbig[:m], want) <= TOL, (tr, slices)
+                assert np.all(Cbig[m:] == 7.25)  # rows beyond m untouched
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_pipeline(4, 4.0e6)
+        gpu_lib.mb200_set_dgemm_mode(1, 0)
+
+
+def test_dgemm_host_pipeline_precision_fallback(gpu_lib):
+    """Chunked 'T' whose product cancels (centred Z^T 1 = 0): some chunk fails the 6-digit bound,
+    the flag travels back with the result and the whole product is redone with 8 digits."""
+    from miraculix_b200 import api
+    snps, indiv, ncol = 16384, 20000, 3
+    plink, Z, f = simulate.simulate(snps, indiv, seed=99)
+    gpu_lib.mb200_set_pipeline(4, 0.0)
+    gpu_lib.mb200_set_dgemm_mode(1, 0)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    sl = C.c_int(0)
+    try:
+        ones = np.ones((indiv, ncol), order="F")
+        got = api.dgemm_compressed("T", h, ones, snps, indiv)
+        assert gpu_lib.mb200_dgemm_last_precision(h, C.byref(sl)) == 2 and sl.value == 8
+        want = cport.dgemm_compressed("T", plink, snps, indiv, f, ones, True)
+        assert np.abs(got - want).max() <= TOL * float(Z.sum(axis=0).max())
+        B = np.asfortranarray(np.random.default_rng(3).standard_normal((snps, ncol)))
+        got = api.dgemm_compressed("N", h, B, snps, indiv)
+        assert gpu_lib.mb200_dgemm_last_precision(h, C.byref(sl)) == 1 and sl.value == 6
+        assert relerr(got, cport.dgemm_compressed("N", plink, snps, indiv, f, B, True)) <= TOL
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_pipeline(4, 4.0e6)
