@@ -20,7 +20,7 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream);
+                        cudaStream_t stream, const CpFinish *finish);
 
 static int upload_lut() {
   uint8_t table[256];
@@ -52,19 +52,47 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   int8_t *X8 = nullptr;
   int32_t *C32 = nullptr;
   double *d_m = nullptr;
+  unsigned int *d_s = nullptr;
   TileCoord *d_tiles = nullptr;
   int num_tiles = 0;
+  const int tc = options().crossprod_mode == 1;
+  const int nslabs = (int)ceil_div(nb, slab_kbytes);
+  // tensor-core path: the last slab's GEMM epilogue writes the final fp64 matrix itself (counts,
+  // or the centred/scaled GRM), so the int32 matrix only exists when K needs several slabs
+  const bool need_c32 = !tc || nslabs > 1;
   cudaEvent_t e0, e1, e2;
   MB_CUDA(cudaEventCreate(&e0));
   MB_CUDA(cudaEventCreate(&e1));
   MB_CUDA(cudaEventCreate(&e2));
   MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
-  MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
+  if (need_c32) MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
-  const int tc = options().crossprod_mode == 1;
   if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream));
 
   MB_CUDA(cudaEventRecord(e0, stream));
+  // GRM: the row sums m = M 1 come exactly from the input, m = X (X^T 1) (64-bit integers), so
+  // the centring can be applied while the counts leave the accumulators.
+  if (mode == 1) {
+    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
+    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, stream));
+    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
+    count_launch();
+    if (do_scale) {
+      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
+      count_launch();
+    }
+    MB_LAUNCH_CHECK();
+  }
+  MB_CUDA(cudaEventRecord(e1, stream));  // [e0,e1) = row sums ("epilogue" time), [e1,e2) = GEMM
+  CpFinish fin;
+  fin.kind = 1;
+  fin.affine = mode == 1;
+  fin.do_scale = do_scale;
+  fin.n = rows;
+  fin.out = d_ans;
+  fin.m = d_m;
+  fin.scal = d_m + rows;
   double executed_ops = 0.0;
   int slab = 0;
   for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
@@ -77,7 +105,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     MB_LAUNCH_CHECK();
     if (tc) {
       MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
-                                   sms, stream));
+                                   sms, stream, slab == nslabs - 1 ? &fin : nullptr));
       executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
     } else {
       const unsigned g = (unsigned)(rows_pad / 64);
@@ -87,24 +115,14 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
       executed_ops += 2.0 * 64.0 * 64.0 * (double)kpad * (double)g * (g + 1) / 2.0;
     }
   }
-  MB_CUDA(cudaEventRecord(e1, stream));
-
-  const unsigned tb = (unsigned)ceil_div(rows, 32);
-  counts_to_double_kernel<<<dim3(tb, tb), 256, 0, stream>>>(C32, rows_pad, rows, d_ans);
-  count_launch();
-  MB_LAUNCH_CHECK();
-  if (mode == 1) {  // centred (and scaled) GRM
-    colsum_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(d_ans, rows, d_m);
-    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
-    if (do_scale) {
-      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
-      count_launch();
-    }
-    grm_affine_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_m, d_m + rows, do_scale);
-    count_launch(3);
+  if (!tc) {  // SIMT cross-check path: separate conversion pass
+    const unsigned tb = (unsigned)ceil_div(rows, 32);
+    counts_to_double_kernel<<<dim3(tb, tb), 256, 0, stream>>>(C32, rows_pad, rows, d_ans, mode == 1,
+                                                              d_m, d_m + rows, do_scale);
+    count_launch();
     MB_LAUNCH_CHECK();
-  } else if (mode == 2) {  // LD: rows = SNPs, k = individuals
+  }
+  if (mode == 2) {  // LD: rows = SNPs, k = individuals
     if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for LD");
     ld_rank1_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_f, -4.0 * (double)k, d_m);
     ld_scale_kernel<<<sms * 8, 256, 0, stream>>>(d_ans, rows, d_m);
@@ -114,16 +132,17 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   MB_CUDA(cudaEventRecord(e2, stream));
 
   MB_CUDA(cudaFreeAsync(X8, stream));
-  MB_CUDA(cudaFreeAsync(C32, stream));
+  if (C32) MB_CUDA(cudaFreeAsync(C32, stream));
   MB_CUDA(cudaFreeAsync(d_m, stream));
+  if (d_s) MB_CUDA(cudaFreeAsync(d_s, stream));
   if (d_tiles) MB_CUDA(cudaFreeAsync(d_tiles, stream));
   MB_CUDA(cudaStreamSynchronize(stream));
   if (timing) {
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);
     cudaEventElapsedTime(&b, e1, e2);
-    timing->gemm_ms = a;
-    timing->epilogue_ms = b;
+    timing->gemm_ms = b;      // expand + GEMM with the fused fp64 epilogue (+ LD passes)
+    timing->epilogue_ms = a;  // row sums from the input (GRM only)
     timing->executed_ops = executed_ops;
   }
   cudaEventDestroy(e0);
@@ -171,7 +190,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   int8_t *X8 = nullptr;
   int32_t *C32 = nullptr;
   double *d_m = nullptr;
-  unsigned long long *d_s = nullptr;
+  unsigned int *d_s = nullptr;
   TileCoord *d_tiles = nullptr;
   int num_tiles = 0;
   cudaEvent_t e0, e1, e2;
@@ -179,11 +198,38 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   MB_CUDA(cudaEventCreate(&e1));
   MB_CUDA(cudaEventCreate(&e2));
   MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
-  MB_CUDA(cudaMallocAsync(&C32, (size_t)local_rows * rows_pad * sizeof(int32_t), stream));
+  const int nslabs = (int)ceil_div(nb, slab_kbytes);
+  if (nslabs > 1)  // int32 partials only exist when K needs several slabs
+    MB_CUDA(cudaMallocAsync(&C32, (size_t)local_rows * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
   MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream));
 
   MB_CUDA(cudaEventRecord(e0, stream));
+  if (mode == 1) {
+    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
+    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, stream));
+    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
+    count_launch();
+    if (do_scale) {
+      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
+      count_launch();
+    }
+    MB_LAUNCH_CHECK();
+  }
+  // entries left of a row tile's first computed column tile are not part of the panel: zero
+  MB_CUDA(cudaMemsetAsync(d_panel, 0, sizeof(double) * (size_t)local_rows * rows, stream));
+  MB_CUDA(cudaEventRecord(e1, stream));  // [e0,e1) = row sums + panel clear, [e1,e2) = GEMM
+  CpFinish fin;
+  fin.kind = 2;
+  fin.affine = mode == 1;
+  fin.do_scale = do_scale;
+  fin.part = part;
+  fin.nparts = nparts;
+  fin.n = rows;
+  fin.out = d_panel;
+  fin.m = d_m;
+  fin.scal = d_m + rows;
   double executed_ops = 0.0;
   int slab = 0;
   for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
@@ -194,36 +240,13 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     count_launch();
     MB_LAUNCH_CHECK();
     MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
-                                 slab > 0, sms, stream));
+                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr));
     executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
   }
-  MB_CUDA(cudaEventRecord(e1, stream));
-
-  if (mode == 1) {
-    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned long long) * 4 * nb, stream));
-    MB_CUDA(cudaMemsetAsync(d_s, 0, sizeof(unsigned long long) * 4 * nb, stream));
-    int ysplit = (int)(rows / 512 < 1 ? 1 : rows / 512 > 64 ? 64 : rows / 512);
-    snp_colsum_kernel<<<dim3((unsigned)ceil_div(nb, 256), ysplit), 256, 0, stream>>>(
-        d_x, rows, nb, is_plink_format, d_s);
-    row_dot_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(d_x, rows, nb, is_plink_format,
-                                                                    d_s, d_m);
-    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
-    count_launch(3);
-    if (do_scale) {
-      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
-      count_launch();
-    }
-    MB_LAUNCH_CHECK();
-  }
-  panel_finish_kernel<<<sms * 8, 256, 0, stream>>>(C32, rows_pad, local_rows, rows, part, nparts,
-                                                   mode, d_m, d_m + rows, do_scale, d_panel);
-  count_launch();
-  MB_LAUNCH_CHECK();
   MB_CUDA(cudaEventRecord(e2, stream));
 
   MB_CUDA(cudaFreeAsync(X8, stream));
-  MB_CUDA(cudaFreeAsync(C32, stream));
+  if (C32) MB_CUDA(cudaFreeAsync(C32, stream));
   MB_CUDA(cudaFreeAsync(d_m, stream));
   if (d_s) MB_CUDA(cudaFreeAsync(d_s, stream));
   MB_CUDA(cudaFreeAsync(d_tiles, stream));
@@ -232,8 +255,8 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);
     cudaEventElapsedTime(&b, e1, e2);
-    timing->gemm_ms = a;
-    timing->epilogue_ms = b;
+    timing->gemm_ms = b;
+    timing->epilogue_ms = a;
     timing->executed_ops = executed_ops;
   }
   cudaEventDestroy(e0);

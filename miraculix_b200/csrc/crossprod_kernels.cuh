@@ -55,13 +55,27 @@ expand_2bit_kernel(const uint8_t *__restrict__ x, long rows, long nb, long kb0, 
 }
 
 // int32 counts (row-major, ld32, valid where row <= col) -> fp64 full symmetric column-major
-// n x n (reference host loop src/cuda/snp_multiply_cuda.cu:330-340).  32x32 tiles.
+// n x n (reference host loop src/cuda/snp_multiply_cuda.cu:330-340), 32x32 tiles.  With affine != 0
+// the GRM update of crossproduct.jl:95-106 is applied on the way out, in that operation order
+// (M += (-1/n) m_i ; M += (-1/n) m_j ; M += total/n^2 ; M /= c), each step rounded like the BLAS
+// sequence (no FMA contraction): scal[0] = total = sum m, scal[1] = c = 2 sum f (1 - f).
+__device__ __forceinline__ double grm_affine(double v, double mi, double mj, double alpha,
+                                             double shift, double rc, int do_scale) {
+  v = __dadd_rn(v, __dmul_rn(alpha, mi));
+  v = __dadd_rn(v, __dmul_rn(alpha, mj));
+  v = __dadd_rn(v, shift);
+  return do_scale ? __dmul_rn(v, rc) : v;  // rc = 1/c: one ulp from M / c, no fp64 divide per entry
+}
 __global__ void __launch_bounds__(256)
 counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
-                        double *__restrict__ ans) {
+                        double *__restrict__ ans, int affine, const double *__restrict__ m,
+                        const double *__restrict__ scal, int do_scale) {
   __shared__ int32_t t[32][33];
   const long bi = blockIdx.x, bj = blockIdx.y;  // output tile: rows i in bi, cols j in bj
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const double alpha = -1.0 / (double)n;
+  const double shift = affine ? scal[0] / ((double)n * (double)n) : 0.0;
+  const double c = affine && do_scale ? 1.0 / scal[1] : 1.0;
   if (bi <= bj) {
     // source M32[i][j], contiguous in j: load (i = ty.., j = tx), transpose through smem
     for (int yy = ty; yy < 32; yy += 8) {
@@ -71,13 +85,21 @@ counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
     __syncthreads();
     for (int yy = ty; yy < 32; yy += 8) {
       const long j = bj * 32 + yy, i = bi * 32 + tx;
-      if (i < n && j < n) ans[i + j * n] = (double)t[tx][yy];
+      if (i < n && j < n) {
+        double v = (double)t[tx][yy];
+        if (affine) v = grm_affine(v, m[i], m[j], alpha, shift, c, do_scale);
+        ans[i + j * n] = v;
+      }
     }
   } else {
     // lower tile: value = M32[j][i], contiguous in i -> direct coalesced read and write
     for (int yy = ty; yy < 32; yy += 8) {
       const long j = bj * 32 + yy, i = bi * 32 + tx;
-      if (i < n && j < n) ans[i + j * n] = (double)M32[j * ld32 + i];
+      if (i < n && j < n) {
+        double v = (double)M32[j * ld32 + i];
+        if (affine) v = grm_affine(v, m[i], m[j], alpha, shift, c, do_scale);
+        ans[i + j * n] = v;
+      }
     }
   }
 }
@@ -161,10 +183,11 @@ ld_scale_kernel(double *__restrict__ M, long n, const double *__restrict__ sigma
 __device__ __forceinline__ uint32_t packed_values(uint32_t byte, int is_plink) {
   return is_plink ? c_plink2twobit[byte] : byte;  // 4 fields, each the value 0..3
 }
-// s[4b + t] += sum_r field_t(x[r][b]);  thread = packed byte column, grid.y splits the rows
+// s[4b + t] += sum_r field_t(x[r][b]);  thread = packed byte column, grid.y splits the rows.
+// Sums stay below 3 rows < 2^32.  (Byte path: any nb; the word path below needs nb % 4 == 0.)
 __global__ void __launch_bounds__(256)
 snp_colsum_kernel(const uint8_t *__restrict__ x, long rows, long nb, int is_plink,
-                  unsigned long long *__restrict__ s) {
+                  unsigned int *__restrict__ s) {
   const long b = (long)blockIdx.x * 256 + threadIdx.x;
   if (b >= nb) return;
   const long per = (rows + gridDim.y - 1) / gridDim.y;
@@ -174,26 +197,177 @@ snp_colsum_kernel(const uint8_t *__restrict__ x, long rows, long nb, int is_plin
     const uint32_t v = packed_values(x[r * nb + b], is_plink);
     c0 += v & 3u; c1 += (v >> 2) & 3u; c2 += (v >> 4) & 3u; c3 += (v >> 6) & 3u;
   }
-  if (c0) atomicAdd(&s[4 * b + 0], (unsigned long long)c0);
-  if (c1) atomicAdd(&s[4 * b + 1], (unsigned long long)c1);
-  if (c2) atomicAdd(&s[4 * b + 2], (unsigned long long)c2);
-  if (c3) atomicAdd(&s[4 * b + 3], (unsigned long long)c3);
+  if (c0) atomicAdd(&s[4 * b + 0], c0);
+  if (c1) atomicAdd(&s[4 * b + 1], c1);
+  if (c2) atomicAdd(&s[4 * b + 2], c2);
+  if (c3) atomicAdd(&s[4 * b + 3], c3);
 }
 // m[r] = sum_k x_rk s_k, exact in 64-bit integers (one warp per row)
 __global__ void __launch_bounds__(256)
 row_dot_kernel(const uint8_t *__restrict__ x, long rows, long nb, int is_plink,
-               const unsigned long long *__restrict__ s, double *__restrict__ m) {
+               const unsigned int *__restrict__ s, double *__restrict__ m) {
   const long r = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (r >= rows) return;
   const int lane = threadIdx.x & 31;
   unsigned long long acc = 0;
   for (long b = lane; b < nb; b += 32) {
     const uint32_t v = packed_values(x[r * nb + b], is_plink);
-    acc += (v & 3u) * s[4 * b] + ((v >> 2) & 3u) * s[4 * b + 1] + ((v >> 4) & 3u) * s[4 * b + 2] +
-           ((v >> 6) & 3u) * s[4 * b + 3];
+    acc += (unsigned long long)((v & 3u) * s[4 * b] + ((v >> 2) & 3u) * s[4 * b + 1]) +
+           (unsigned long long)(((v >> 4) & 3u) * s[4 * b + 2] + ((v >> 6) & 3u) * s[4 * b + 3]);
   }
   for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if (lane == 0) m[r] = (double)acc;
+}
+// ---- word variants (rows are whole 32-bit words: nb % 4 == 0, 4-byte aligned base) ----
+__device__ __forceinline__ uint32_t word_values(uint32_t w, int is_plink) {
+  if (!is_plink) return w;
+  return (uint32_t)c_plink2twobit[w & 255u] | ((uint32_t)c_plink2twobit[(w >> 8) & 255u] << 8) |
+         ((uint32_t)c_plink2twobit[(w >> 16) & 255u] << 16) | ((uint32_t)c_plink2twobit[w >> 24] << 24);
+}
+// thread = word column (16 genotypes); the four fields of every byte are counted in four SWAR
+// byte-lane accumulators, flushed every 64 rows (64 x 3 < 256).
+__global__ void __launch_bounds__(128)
+snp_colsum_words_kernel(const uint32_t *__restrict__ x, long rows, long nw, int is_plink,
+                        unsigned int *__restrict__ s) {
+  const long w = (long)blockIdx.x * 128 + threadIdx.x;
+  if (w >= nw) return;
+  const long per = (rows + gridDim.y - 1) / gridDim.y;
+  const long r0 = (long)blockIdx.y * per, r1 = r0 + per < rows ? r0 + per : rows;
+  unsigned int c[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) c[i] = 0;
+  for (long rb = r0; rb < r1; rb += 64) {
+    const long re = rb + 64 < r1 ? rb + 64 : r1;
+    uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (long r = rb; r < re; r++) {
+      const uint32_t v = word_values(x[r * nw + w], is_plink);
+      a0 += v & 0x03030303u;
+      a1 += (v >> 2) & 0x03030303u;
+      a2 += (v >> 4) & 0x03030303u;
+      a3 += (v >> 6) & 0x03030303u;
+    }
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+      c[4 * b + 0] += (a0 >> (8 * b)) & 255u;
+      c[4 * b + 1] += (a1 >> (8 * b)) & 255u;
+      c[4 * b + 2] += (a2 >> (8 * b)) & 255u;
+      c[4 * b + 3] += (a3 >> (8 * b)) & 255u;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 16; i++)
+    if (c[i]) atomicAdd(&s[16 * w + i], c[i]);
+}
+// Byte planes of the column sums for dp4a: word w, field j (genotypes 16w + 4b + j, b = 0..3,
+// i.e. the four byte lanes of (v >> 2j) & 0x03030303) -> planes[(4w + j)] = uint4 whose component
+// p packs bits [8p, 8p+8) of those four sums.  In place over s (same size, one thread per (w, j)
+// group would race) -> separate output.
+__global__ void __launch_bounds__(256)
+colsum_planes_kernel(const unsigned int *__restrict__ s, long nw, uint4 *__restrict__ planes) {
+  const long g = (long)blockIdx.x * 256 + threadIdx.x;  // g = 4 w + j
+  if (g >= 4 * nw) return;
+  const long w = g >> 2;
+  const int j = (int)(g & 3);
+  unsigned int v[4];
+#pragma unroll
+  for (int b = 0; b < 4; b++) v[b] = s[16 * w + 4 * b + j];
+  unsigned int pl[4];
+#pragma unroll
+  for (int p = 0; p < 4; p++)
+    pl[p] = ((v[0] >> (8 * p)) & 255u) | (((v[1] >> (8 * p)) & 255u) << 8) |
+            (((v[2] >> (8 * p)) & 255u) << 16) | (((v[3] >> (8 * p)) & 255u) << 24);
+  planes[g] = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+}
+// m[r] = sum_k x_rk s_k with u8 x u8 dot products (dp4a) against the byte planes: one warp per 8
+// rows, the planes of a word are loaded once and applied to the 8 rows; each plane accumulates in
+// 32 bits (<= 4 x 3 x 255 per dp4a, 4 per word, nw/32 words per lane), combined in 64 bits.
+constexpr int RD_ROWS = 8;
+__global__ void __launch_bounds__(256)
+row_dot_words_kernel(const uint32_t *__restrict__ x, long rows, long nw, int is_plink,
+                     const uint4 *__restrict__ planes, double *__restrict__ m) {
+  const long r0 = ((long)blockIdx.x * 8 + (threadIdx.x >> 5)) * RD_ROWS;
+  if (r0 >= rows) return;
+  const int lane = threadIdx.x & 31;
+  unsigned int acc[RD_ROWS][4];
+#pragma unroll
+  for (int q = 0; q < RD_ROWS; q++)
+#pragma unroll
+    for (int p = 0; p < 4; p++) acc[q][p] = 0;
+  unsigned long long tot[RD_ROWS];
+#pragma unroll
+  for (int q = 0; q < RD_ROWS; q++) tot[q] = 0;
+  long it = 0;
+  const long wper = (nw + gridDim.y - 1) / gridDim.y;
+  const long w1 = (blockIdx.y + 1) * wper < nw ? (blockIdx.y + 1) * wper : nw;
+  for (long w = blockIdx.y * wper + lane; w < w1; w += 32, it++) {
+    uint4 pl[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) pl[j] = planes[4 * w + j];
+    uint32_t xv[RD_ROWS];  // all loads first (rows past the end re-read the last row, discarded)
+#pragma unroll
+    for (int q = 0; q < RD_ROWS; q++) {
+      const long rr = r0 + q < rows ? r0 + q : rows - 1;
+      xv[q] = x[rr * nw + w];
+    }
+#pragma unroll
+    for (int q = 0; q < RD_ROWS; q++) {
+      const uint32_t v = word_values(xv[q], is_plink);
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const uint32_t g = (v >> (2 * j)) & 0x03030303u;
+        acc[q][0] = __dp4a(g, pl[j].x, acc[q][0]);
+        acc[q][1] = __dp4a(g, pl[j].y, acc[q][1]);
+        acc[q][2] = __dp4a(g, pl[j].z, acc[q][2]);
+        acc[q][3] = __dp4a(g, pl[j].w, acc[q][3]);
+      }
+    }
+    if ((it & 65535) == 65535) {  // 32-bit headroom: 65536 x 4 x 3060 < 2^32
+#pragma unroll
+      for (int q = 0; q < RD_ROWS; q++) {
+#pragma unroll
+        for (int p = 0; p < 4; p++) { tot[q] += (unsigned long long)acc[q][p] << (8 * p); acc[q][p] = 0; }
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < RD_ROWS; q++) {
+    unsigned long long a = tot[q];
+#pragma unroll
+    for (int p = 0; p < 4; p++) a += (unsigned long long)acc[q][p] << (8 * p);
+    for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    // integer partials below 2^53: the fp64 atomic sum over the K splits is exact in any order
+    if (lane == 0 && r0 + q < rows) atomicAdd(&m[r0 + q], (double)a);
+  }
+}
+// m = X (X^T 1) for a packed matrix x[rows][nb]; d_s: input_row_sums_scratch(nb) unsigned ints
+inline size_t input_row_sums_scratch(long nb) { return 2 * (size_t)(4 * nb + 16); }
+inline int input_row_sums(const uint8_t *d_x, long rows, long nb, int is_plink, unsigned int *d_s,
+                          double *d_m, cudaStream_t stream) {
+  MB_CUDA(cudaMemsetAsync(d_s, 0, sizeof(unsigned int) * (4 * nb + 16), stream));
+  int ysplit = (int)(rows / 512 < 1 ? 1 : rows / 512 > 64 ? 64 : rows / 512);
+  if (nb % 4 == 0 && (reinterpret_cast<uintptr_t>(d_x) & 15) == 0) {
+    const long nw = nb / 4;
+    ysplit = (int)(ceil_div(rows, 128) > 4096 ? 4096 : ceil_div(rows, 128));  // <= 2 flushes per thread
+    snp_colsum_words_kernel<<<dim3((unsigned)ceil_div(nw, 128), ysplit), 128, 0, stream>>>(
+        reinterpret_cast<const uint32_t *>(d_x), rows, nw, is_plink, d_s);
+    uint4 *planes = reinterpret_cast<uint4 *>(d_s + 4 * nb + 16);  // 16-byte aligned: nb % 4 == 0
+    colsum_planes_kernel<<<(unsigned)ceil_div(4 * nw, 256), 256, 0, stream>>>(d_s, nw, planes);
+    const long rblocks = ceil_div(rows, 8 * RD_ROWS);
+    long ks = ceil_div(148 * 6, rblocks);
+    if (ks > ceil_div(nw, 256)) ks = ceil_div(nw, 256);
+    if (ks < 1) ks = 1;
+    MB_CUDA(cudaMemsetAsync(d_m, 0, sizeof(double) * rows, stream));
+    row_dot_words_kernel<<<dim3((unsigned)rblocks, (unsigned)ks), 256, 0, stream>>>(
+        reinterpret_cast<const uint32_t *>(d_x), rows, nw, is_plink, planes, d_m);
+    count_launch();
+  } else {
+    snp_colsum_kernel<<<dim3((unsigned)ceil_div(nb, 256), ysplit), 256, 0, stream>>>(d_x, rows, nb,
+                                                                                     is_plink, d_s);
+    row_dot_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(d_x, rows, nb, is_plink, d_s, d_m);
+  }
+  count_launch(2);
+  MB_LAUNCH_CHECK();
+  return 0;
 }
 // Compact panel of one partition: local row lr is global row ((lr/128) nparts + part) 128 + lr%128.
 // Columns left of the first computed tile (256 floor(i/256)) are not part of the panel: zero.
@@ -205,7 +379,7 @@ panel_finish_kernel(const int32_t *__restrict__ C32, long ld32, long local_rows,
   const long total = local_rows * n;
   const double alpha = -1.0 / (double)n;
   const double shift = mode ? scal[0] / ((double)n * (double)n) : 0.0;
-  const double c = mode ? scal[1] : 1.0;
+  const double rc = mode && do_scale ? 1.0 / scal[1] : 1.0;
   for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
        e += (long)gridDim.x * blockDim.x) {
     const long lr = e / n, j = e % n;
@@ -213,12 +387,7 @@ panel_finish_kernel(const int32_t *__restrict__ C32, long ld32, long local_rows,
     double v = 0.0;
     if (i < n && j >= ((i >> 8) << 8)) {
       v = (double)C32[lr * ld32 + j];
-      if (mode) {
-        v = __dadd_rn(v, __dmul_rn(alpha, m[i]));
-        v = __dadd_rn(v, __dmul_rn(alpha, m[j]));
-        v = __dadd_rn(v, shift);
-        if (do_scale) v = v / c;
-      }
+      if (mode) v = grm_affine(v, m[i], m[j], alpha, shift, rc, do_scale);
     }
     out[e] = v;
   }

@@ -28,6 +28,14 @@ constexpr int TC_STAGE_BYTES = TC_A_BYTES + TC_B_BYTES;
 constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int TC_THREADS = 192;
 
+__device__ __forceinline__ double cp_affine(double v, double mr, double mc, double alpha,
+                                            double shift, double rc, int do_scale) {
+  v = __dadd_rn(v, __dmul_rn(alpha, mr));  // same operation order as grm_affine (crossprod_kernels.cuh)
+  v = __dadd_rn(v, __dmul_rn(alpha, mc));
+  v = __dadd_rn(v, shift);
+  return do_scale ? __dmul_rn(v, rc) : v;
+}
+
 struct TileCoord {
   int mi, nj;  // operand tiles: rows mi*128.. of X against rows nj*256.. of X
   int mo;      // output row tile: C32 row = mo*128 + r (== mi unless the output is a compact
@@ -38,7 +46,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b,
                     const TileCoord *__restrict__ tiles, int num_tiles, int num_kblocks,
-                    int32_t *__restrict__ C32, long ld32, int accumulate) {
+                    int32_t *__restrict__ C32, long ld32, int accumulate, const CpFinish fin) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
@@ -120,6 +128,9 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int quad = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
+    const double alpha = fin.kind ? -1.0 / (double)fin.n : 0.0;
+    const double shift = fin.affine ? fin.scal[0] / ((double)fin.n * (double)fin.n) : 0.0;
+    const double rc = fin.affine && fin.do_scale ? 1.0 / fin.scal[1] : 1.0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const TileCoord tc = tiles[t];
       mbar_wait(&tfull[acc], acc_phase);
@@ -127,21 +138,77 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const long row = (long)tc.mo * TC_BM + quad * 32 + lane;
       int32_t *crow = C32 + row * ld32 + (long)tc.nj * TC_BN;
       const uint32_t taddr = tmem_base + acc * TC_BN + ((uint32_t)(quad * 32) << 16);
+      // global row of the result this thread owns (panels are compact in the row tiles)
+      const long gi = fin.kind == 2 ? ((long)tc.mo * fin.nparts + fin.part) * TC_BM + quad * 32 + lane
+                                    : row;
+      const bool iok = fin.kind && gi < fin.n;
+      const double mi = (fin.affine && iok) ? fin.m[gi] : 0.0;
 #pragma unroll 1
       for (int c = 0; c < TC_BN / 32; c++) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr + c * 32, r);
         tmem_ld_wait();
-        int4 *dst = reinterpret_cast<int4 *>(crow + c * 32);
+        if (fin.kind == 0) {
+          int4 *dst = reinterpret_cast<int4 *>(crow + c * 32);
 #pragma unroll
-        for (int q = 0; q < 8; q++) {
-          int4 v = make_int4((int)r[4 * q], (int)r[4 * q + 1], (int)r[4 * q + 2], (int)r[4 * q + 3]);
-          if (accumulate) {
-            const int4 o = dst[q];
-            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          for (int q = 0; q < 8; q++) {
+            int4 v = make_int4((int)r[4 * q], (int)r[4 * q + 1], (int)r[4 * q + 2], (int)r[4 * q + 3]);
+            if (accumulate) {
+              const int4 o = dst[q];
+              v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+            }
+            dst[q] = v;
           }
-          dst[q] = v;
+          continue;
         }
+        if (accumulate) {
+          const int4 *src = reinterpret_cast<const int4 *>(crow + c * 32);
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            const int4 o = src[q];
+            r[4 * q] += (uint32_t)o.x; r[4 * q + 1] += (uint32_t)o.y;
+            r[4 * q + 2] += (uint32_t)o.z; r[4 * q + 3] += (uint32_t)o.w;
+          }
+        }
+        const long j0 = (long)tc.nj * TC_BN + c * 32;
+        // row sums of this chunk's 32 columns: one per lane (read-only path), broadcast by shuffle
+        // -- a plain m[j] load inside the store loop is serialised behind the stores (aliasing)
+        const double mlane = (fin.affine && j0 + lane < fin.n) ? __ldg(fin.m + j0 + lane) : 0.0;
+        double mjv[32];
+#pragma unroll
+        for (int q = 0; q < 32; q++) mjv[q] = __shfl_sync(0xffffffffu, mlane, q);
+        if (!iok) {
+          // padding row: nothing to write (stay converged for the next collective tcgen05.ld)
+        } else if (fin.kind == 1) {
+          double *col = fin.out + gi + j0 * fin.n;      // (i, j0 + q): lanes = consecutive i
+          double *mir = fin.out + j0 + gi * fin.n;      // (j0 + q, i): this thread's own column
+#pragma unroll
+          for (int q = 0; q < 32; q++) {
+            const long j = j0 + q;
+            if (j < fin.n && gi <= j) {
+              const double v = (double)(int)r[q];
+              if (fin.affine) {
+                const double mj = mjv[q];
+                col[(long)q * fin.n] = cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale);
+                mir[q] = cp_affine(v, mj, mi, alpha, shift, rc, fin.do_scale);
+              } else {
+                col[(long)q * fin.n] = v;
+                mir[q] = v;
+              }
+            }
+          }
+        } else {
+          double *prow = fin.out + row * fin.n + j0;
+#pragma unroll
+          for (int q = 0; q < 32; q++) {
+            const long j = j0 + q;
+            if (j < fin.n) {
+              const double v = (double)(int)r[q];
+              prow[q] = fin.affine ? cp_affine(v, mi, mjv[q], alpha, shift, rc, fin.do_scale) : v;
+            }
+          }
+        }
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
@@ -220,7 +287,7 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, const CpFinish *finish) {
   MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                TC_SMEM));
   CUtensorMap ta, tb;
@@ -230,7 +297,7 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
   const int grid = num_tiles < sm_count ? num_tiles : sm_count;
   crossprod_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
                                                              (int)(kcols / TC_BK), C32, ld32,
-                                                             accumulate);
+                                                             accumulate, finish ? *finish : CpFinish());
   count_launch();
   MB_LAUNCH_CHECK();
   return 0;

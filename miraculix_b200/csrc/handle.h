@@ -103,6 +103,22 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
 int dgemm_tc_read_trace(long long *out, int n);
 int dgemm_tc_last_precision(Handle *h, int *slices);  // dgemm_tc.cu, MB200_TRACE=1
 
+// What the epilogue does with a finished accumulator tile.  kind 0: store int32 counts into C32
+// (+= when accumulating K slabs).  kind 1/2 (last K slab): convert to fp64 -- adding the int32
+// partial of earlier slabs when accumulating -- apply the GRM centring/scaling of
+// crossproduct.jl:95-106 on the way out (affine) and write the final result directly:
+//   1: full symmetric column-major n x n matrix: every upper entry (i <= j) goes to (i,j) and (j,i)
+//   2: compact row-major panel [local rows][n] of one partition's row tiles (crossprod.cu)
+struct CpFinish {
+  int kind = 0;
+  int affine = 0, do_scale = 0;
+  int part = 0, nparts = 1;
+  long n = 0;
+  double *out = nullptr;
+  const double *m = nullptr;     // row sums of the count matrix
+  const double *scal = nullptr;  // [0] = sum m, [1] = 2 sum f (1 - f)
+};
+
 // crossprod.cu
 struct CrossprodTiming {
   double gemm_ms = 0, epilogue_ms = 0, executed_ops = 0;
