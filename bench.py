@@ -186,6 +186,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=dev)
     build.build()
     lib = api.load_library()
@@ -270,13 +272,8 @@ def run_ours(args):
             lib.dgemm_compressed(b"N", handle, ncol, hBn.data_ptr(), snps, hCn.data_ptr(), indiv)
             lib.dgemm_compressed(b"T", handle, ncol, hBt.data_ptr(), indiv, hCt.data_ptr(), snps)
         else:
-            with torch.cuda.stream(stream):
-                Bn.copy_(hBn, non_blocking=True)
-                sh.dgemm_n(Bn, Cn)
-                hCn.copy_(Cn, non_blocking=True)
-                Bt.copy_(hBt, non_blocking=True)
-                sh.dgemm_t(Bt, Ct)
-                hCt.copy_(Ct, non_blocking=True)
+            sh.dgemm_n_host(hBn, Cn, hCn)   # pipelined upload, device all-reduce, async download
+            sh.dgemm_t_host(hBt, hCt)       # the C-ABI call on the shard, pipelined download
             stream.synchronize()
 
     e2e_steps = max(2, min(args.steps, 5))
@@ -352,7 +349,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "ms_per_step": e2e_ms / e2e_steps,
                     "api": "dgemm_compressed() C-ABI with pinned host B/C" if world == 1 else
-                           "ShardedCompressed with pinned host B/C + NCCL all-reduce"},
+                           "ShardedCompressed.dgemm_n_host/dgemm_t_host: pinned host B/C, pipelined PCIe, NCCL all-reduce"},
             "gpu_launches": int(launches), "clocks": clocks}
 
     if pcg is not None:
@@ -548,6 +545,18 @@ def run_cpu_baseline(args):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: anything libraries print while we run (NCCL's version
+    # banner, torchrun notices) is routed to stderr, and the line goes to the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    import builtins
+    _print = builtins.print
+
+    def emit(*a, **kw):
+        text = " ".join(str(x) for x in a) + kw.get("end", "\n")
+        os.write(real_stdout, text.encode())
+    builtins.print = emit
     if args.impl == "reference":
         run_reference(args)
     else:

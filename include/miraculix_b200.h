@@ -98,6 +98,12 @@ int mb200_set_crossprod_mode(int mode);
  * handle's stream (mb200_stream).  trans: 0 = 'N', 1 = 'T'.  Returns 0 / error code. */
 int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
                                   double *dC, long ldc);
+/* Same product with each panel on the host OR on the device (flags): host panels are copied over
+ * PCIe, pipelined against the kernels like dgemm_compressed.  Blocking (returns after the
+ * handle's stream has drained) unless both panels are on the device.  Used by SNP-sharded callers:
+ * 'N' with B on the host and C on the device (the partial is all-reduced before it goes home). */
+int mb200_dgemm_compressed_mixed(int trans, void *compressed, int n, const double *B, long ldb,
+                                 int b_on_device, double *C, long ldc, int c_on_device);
 void *mb200_stream(void *compressed); /* cudaStream_t */
 /* Device time of the MAIN kernel of the last dgemm_compressed call on this handle (CUDA events
  * recorded on the handle's stream around that one launch); synchronises the stream. */

@@ -44,6 +44,8 @@ SIGNATURES = {
     "mb200_set_pipeline": (C.c_int, [C.c_int, C.c_double]),
     "mb200_dgemm_compressed_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
                                                 C.c_void_p, C.c_long]),
+    "mb200_dgemm_compressed_mixed": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
+                                               C.c_int, C.c_void_p, C.c_long, C.c_int]),
     "mb200_stream": (C.c_void_p, [C.c_void_p]),
     "mb200_sync": (C.c_int, [C.c_void_p]),
     "mb200_dgemm_last_precision": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),

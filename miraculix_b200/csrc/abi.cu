@@ -405,7 +405,7 @@ static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, do
                 ldb, k, ldc, m);
   if (n <= 0) return 0;
   if (options().dgemm_mode == 1)  // tensor-core path: PCIe copies pipelined against the kernels
-    return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc);
+    return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc, 0, 0);
   if (ldb == k)
     MB_CUDA(cudaMemcpyAsync(h->d_B, B, sizeof(double) * k * n, cudaMemcpyHostToDevice, h->stream));
   else
@@ -417,6 +417,40 @@ static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, do
   else
     MB_CUDA(cudaMemcpy2DAsync(C, sizeof(double) * ldc, h->d_C, sizeof(double) * m,
                               sizeof(double) * m, n, cudaMemcpyDeviceToHost, h->stream));
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+// B and/or C may live on the device (SNP-sharded callers reduce the 'N' partial on the device
+// before it goes back to the host); host panels are copied, pipelined where it pays.
+int mb200_dgemm_compressed_mixed(int trans, void *compressed, int n, const double *B, long ldb,
+                                 int b_on_device, double *C, long ldc, int c_on_device) {
+  clear_status();
+  Handle *h = as_handle(compressed);
+  if (!h) return status().code;
+  trans = trans ? 1 : 0;
+  const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
+  if (n < 0 || n > h->max_n || ldb < k || ldc < m)
+    return fail(-2, __func__, __LINE__, "bad arguments n=%d (max_n=%d) ldb=%ld (k=%ld) ldc=%ld (m=%ld)",
+                n, h->max_n, ldb, k, ldc, m);
+  if (n == 0) return 0;
+  if (b_on_device && c_on_device) return dgemm_device(h, trans, n, B, ldb, C, ldc);
+  if (options().dgemm_mode == 1)
+    return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc, b_on_device, c_on_device);
+  // fp64 SIMT family: plain staging
+  const double *dB = B;
+  double *dC = C;
+  if (!b_on_device) {
+    MB_CUDA(cudaMemcpy2DAsync(h->d_B, sizeof(double) * k, B, sizeof(double) * ldb, sizeof(double) * k,
+                              n, cudaMemcpyHostToDevice, h->stream));
+    dB = h->d_B;
+    ldb = k;
+  }
+  if (!c_on_device) dC = h->d_C;
+  MB_CHECK(dgemm_device(h, trans, n, dB, ldb, dC, c_on_device ? ldc : m));
+  if (!c_on_device)
+    MB_CUDA(cudaMemcpy2DAsync(C, sizeof(double) * ldc, h->d_C, sizeof(double) * m, sizeof(double) * m,
+                              n, cudaMemcpyDeviceToHost, h->stream));
   MB_CUDA(cudaStreamSynchronize(h->stream));
   return 0;
 }

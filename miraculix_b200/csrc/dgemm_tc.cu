@@ -623,9 +623,16 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
 // (rare) redoes the whole product with 8 digits, unchunked.
 // ---------------------------------------------------------------------------------------------
 int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
-                            long ldc) {
+                            long ldc, int b_dev, int c_dev) {
   MB_CHECK(ensure_bq(h));
   const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
+  // panels that already live on the device are used in place; only host panels are copied
+  const double *dB = b_dev ? B : h->d_B;
+  const long ldB = b_dev ? ldb : k;
+  double *dC = c_dev ? C : h->d_C;
+  const long ldC = c_dev ? ldc : m;
+  const bool pipe_in = !trans && !b_dev;   // snps x n panel B uploaded in chunks
+  const bool pipe_out = trans && !c_dev;   // snps x n panel C downloaded in chunks
   const DgemmView full = full_view(h, trans);
   bool adaptive = false, first_main = true;
   const int S = tc_digits(n, full.rows, full.K, &adaptive);
@@ -638,6 +645,7 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   int chunks = options().pipe_chunks;
   if (chunks > Handle::kPipeMax) chunks = Handle::kPipeMax;
   if (chunks < 1 || (double)h->snps * n * 8.0 < options().pipe_min_bytes) chunks = 1;
+  if (!pipe_in && !pipe_out) chunks = 1;
   long per = round_up(ceil_div(h->snps, chunks), 512);
   chunks = (int)ceil_div(h->snps, per);
   int *h_flag = reinterpret_cast<int *>(h->h_pipe);
@@ -651,33 +659,38 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
                              sizeof(double) * rows, cols, kind, st);
   };
 
+  if (!b_dev && !pipe_in)
+    MB_CUDA(copy2d(h->d_B, k, B, ldb, k, n, cudaMemcpyHostToDevice, h->stream));
   if (!trans) {
     MB_CUDA(cudaMemsetAsync(tc_amax_all(h), 0, sizeof(unsigned long long) * n, h->stream));
     for (int i = 0; i < chunks; i++) {
       const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
-      MB_CUDA(copy2d(h->d_B + s0, k, B + s0, ldb, cnt, n, cudaMemcpyHostToDevice, h->copy_stream));
-      MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
-      MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
+      if (pipe_in) {
+        MB_CUDA(copy2d(h->d_B + s0, k, B + s0, ldb, cnt, n, cudaMemcpyHostToDevice, h->copy_stream));
+        MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
+        MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
+      }
       DgemmView v = sub_view(h, 0, s0, cnt);
       v.accumulate = i > 0;
-      MB_CHECK(tc_pass(h, v, n, h->d_B + s0, k, h->d_C, m, S, 0, nullptr, tc_amax_all(h),
-                       &first_main, ev));
+      MB_CHECK(tc_pass(h, v, n, dB + s0, ldB, dC, ldC, S, 0, nullptr, tc_amax_all(h), &first_main, ev));
     }
-    if (adaptive) MB_CHECK(tc_check(h, h->d_C, m, m, n, S, tc_amax_all(h), full.rowsum_max));
-    MB_CUDA(copy2d(C, ldc, h->d_C, m, m, n, cudaMemcpyDeviceToHost, h->stream));
+    if (adaptive) MB_CHECK(tc_check(h, dC, ldC, m, n, S, tc_amax_all(h), full.rowsum_max));
   } else {
-    MB_CUDA(copy2d(h->d_B, k, B, ldb, k, n, cudaMemcpyHostToDevice, h->stream));
     for (int i = 0; i < chunks; i++) {
       const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
       const DgemmView v = sub_view(h, 1, s0, cnt);
-      MB_CHECK(tc_pass(h, v, n, h->d_B, k, h->d_C + s0, m, S, 0, nullptr, nullptr, &first_main, ev));
+      MB_CHECK(tc_pass(h, v, n, dB, ldB, dC + s0, ldC, S, 0, nullptr, nullptr, &first_main, ev));
       if (adaptive)
-        MB_CHECK(tc_check(h, h->d_C + s0, m, cnt, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
-      MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->stream));
-      MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
-      MB_CUDA(copy2d(C + s0, ldc, h->d_C + s0, m, cnt, n, cudaMemcpyDeviceToHost, h->copy_stream));
+        MB_CHECK(tc_check(h, dC + s0, ldC, cnt, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
+      if (pipe_out) {
+        MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->stream));
+        MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
+        MB_CUDA(copy2d(C + s0, ldc, dC + s0, ldC, cnt, n, cudaMemcpyDeviceToHost, h->copy_stream));
+      }
     }
   }
+  if (!c_dev && !pipe_out)
+    MB_CUDA(copy2d(C, ldc, dC, ldC, m, n, cudaMemcpyDeviceToHost, h->stream));
   if (adaptive)
     MB_CUDA(cudaMemcpyAsync(h_flag, tc_flag(h), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
@@ -686,8 +699,8 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   MB_CUDA(cudaStreamSynchronize(h->copy_stream));
   if (adaptive && *h_flag) {  // bound failed somewhere: exact-to-2^-62 redo, everything resident
     first_main = false;
-    MB_CHECK(tc_pass(h, full, n, h->d_B, k, h->d_C, m, 8, 1, nullptr, nullptr, &first_main, ev));
-    MB_CUDA(copy2d(C, ldc, h->d_C, m, m, n, cudaMemcpyDeviceToHost, h->stream));
+    MB_CHECK(tc_pass(h, full, n, dB, ldB, dC, ldC, 8, 1, nullptr, nullptr, &first_main, ev));
+    if (!c_dev) MB_CUDA(copy2d(C, ldc, dC, ldC, m, n, cudaMemcpyDeviceToHost, h->stream));
     MB_CUDA(cudaStreamSynchronize(h->stream));
     h->last_slices = 8;
   }

@@ -98,7 +98,7 @@ int rowsum_maxima(Handle *h);     // fills h->rowsum_max (synchronises the strea
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
 // Host panels B, C: copies pipelined against the kernels in SNP chunks (dgemm_tc.cu)
 int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
-                            long ldc);
+                            long ldc, int b_dev, int c_dev);
 
 int dgemm_tc_read_trace(long long *out, int n);
 int dgemm_tc_last_precision(Handle *h, int *slices);  // dgemm_tc.cu, MB200_TRACE=1

@@ -99,6 +99,43 @@ class ShardedCompressed:
             self._local(1, B, C_local)
         return C_local
 
+    # -- the same two directions with HOST panels (pinned CPU tensors) -------------------------
+    def dgemm_n_host(self, hB_local, C_dev, hC):
+        """'N' end to end: hB_local (n, |S_g|) host rows of B of this rank -> hC (n, indiv) host.
+        The upload is pipelined against the kernels inside the library
+        (mb200_dgemm_compressed_mixed: B on the host, partial C on the device), the partial is
+        all-reduced on the device, then downloaded asynchronously on the library's stream (the
+        next blocking call or stream().synchronize() completes it)."""
+        import torch
+        import torch.distributed as dist
+        from . import api
+        lib = api.load_library()
+        n = hB_local.shape[0]
+        if self.s_count > 0:
+            rc = lib.mb200_dgemm_compressed_mixed(0, self.handle, n, C.c_void_p(hB_local.data_ptr()),
+                                                  hB_local.shape[1], 0, C.c_void_p(C_dev.data_ptr()),
+                                                  C_dev.shape[1], 1)
+            api._check(rc, "mb200_dgemm_compressed_mixed")
+        else:
+            C_dev.zero_()
+        with torch.cuda.stream(self.stream()):
+            if self.world > 1:
+                dist.all_reduce(C_dev, op=dist.ReduceOp.SUM, group=self.group)
+            hC.copy_(C_dev, non_blocking=True)
+        return hC
+
+    def dgemm_t_host(self, hB, hC_local):
+        """'T' end to end: hB (n, indiv) host, replicated -> hC_local (n, |S_g|) host rows S_g.
+        The reference-facing dgemm_compressed() itself on this rank's shard: no exchange, the
+        download of C is pipelined against the kernels.  Blocking."""
+        from . import api
+        lib = api.load_library()
+        if self.s_count > 0:
+            lib.dgemm_compressed(b"T", self.handle, hB.shape[0], hB.data_ptr(), hB.shape[1],
+                                 hC_local.data_ptr(), hC_local.shape[1])
+            api._check(lib.mb200_last_status(), "dgemm_compressed")
+        return hC_local
+
     # -- conjugate gradients over the shards ------------------------------------------------
     def cg_solve(self, b, x, lam: float = 0.0, tol: float = 1e-2, max_iter: int = 1000):
         """(Zc Zc^T + lam I) x = b with the matrix SNP-sharded over the ranks (BASELINE

@@ -268,3 +268,38 @@ def test_dgemm_host_pipeline_precision_fallback(gpu_lib):
     finally:
         api.free_compressed(h)
         gpu_lib.mb200_set_pipeline(4, 4.0e6)
+
+
+@pytest.mark.parametrize("b_dev,c_dev", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_dgemm_mixed_host_device_panels(gpu_lib, b_dev, c_dev):
+    """mb200_dgemm_compressed_mixed: each panel on the host or on the device, chunked pipeline
+    forced on, both directions and both kernel families, against the oracle."""
+    import torch
+    from miraculix_b200 import api
+    snps, indiv, ncol = 6000, 900, 5
+    plink, Z, f = simulate.simulate(snps, indiv, seed=31, missing=0.01)
+    rng = np.random.default_rng(32)
+    gpu_lib.mb200_set_pipeline(3, 0.0)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    try:
+        for mode in (1, 0):
+            gpu_lib.mb200_set_dgemm_mode(mode, 0)
+            for tr, k, m in ((0, snps, indiv), (1, indiv, snps)):
+                B = np.asfortranarray(rng.standard_normal((k, ncol)))
+                want = cport.dgemm_compressed("NT"[tr], plink, snps, indiv, f, B, True)
+                tB = torch.from_numpy(np.ascontiguousarray(B.T))          # (ncol, k) = column-major k x ncol
+                tC = torch.full((ncol, m), 3.5, dtype=torch.float64)
+                if b_dev:
+                    tB = tB.cuda()
+                if c_dev:
+                    tC = tC.cuda()
+                rc = gpu_lib.mb200_dgemm_compressed_mixed(tr, h, ncol, C.c_void_p(tB.data_ptr()), k, b_dev,
+                                                          C.c_void_p(tC.data_ptr()), m, c_dev)
+                assert rc == 0, gpu_lib.mb200_last_message()
+                gpu_lib.mb200_sync(h)
+                got = tC.cpu().numpy().T
+                assert relerr(got, want) <= TOL, (mode, tr)
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_pipeline(4, 4.0e6)
+        gpu_lib.mb200_set_dgemm_mode(1, 0)
