@@ -178,6 +178,17 @@ int mb200_grm_partition(unsigned char *snp_matrix, int snps, int indiv, bool is_
 int mb200_crossprod_last_timing(double out[3]);
 
 /* ------------------------------------------------------------------------------------------
+ * PLINK .bed ingest.  Replaces read_bed (src/bindings/Julia/read_plink.jl:
+ * 161-228) + transpose_genotype_matrix (compressed_operations.jl:45-66) + plink2compressed: the
+ * file `<stem>.bed` (with `<stem>.bim` / `<stem>.fam`, whose line counts give snps / indiv) is
+ * checked like read_bed (suffix, companions, magic 6c 1b 01, exact size), streamed through pinned
+ * buffers and repacked on the GPU chunk by chunk; the allele frequencies are read_bed's
+ * calc_freq rule, set bits per SNP / (2 indiv), and can be fetched with get_compressed_freq.
+ * Error codes: -20 not .bed, -21 missing .bim/.fam, -23 bad magic, -25 too small, -26 too large. */
+int mb200_bed_shape(const char *bed_path, long *snps, long *indiv); /* validation only, no GPU */
+int mb200_read_bed(const char *bed_path, int max_n, void **compressed, long *snps, long *indiv);
+
+/* ------------------------------------------------------------------------------------------
  * Device-resident conjugate gradients (BASELINE configs[3]).
  * Replaces the host loop of examples/iterative_solver/grm_solve_cg.jl:109-133 (GRM_vec :75-85):
  * solves (Zc Zc^T + lambda I) x = b, Zc = Z - 2 1 f^T (or raw Z with do_not_center), with the

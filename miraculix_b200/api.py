@@ -68,6 +68,9 @@ SIGNATURES = {
     "mb200_grm_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_bool, C.c_int, C.c_void_p,
                                       C.c_bool, C.c_int, C.c_int, C.c_void_p]),
     "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
+    "mb200_bed_shape": (C.c_int, [C.c_char_p, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
+    "mb200_read_bed": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_long),
+                                 C.POINTER(C.c_long)]),
     "mb200_cg_solve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                         C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int),
                                         C.POINTER(C.c_double)]),
@@ -253,6 +256,23 @@ def grm_partition(x: np.ndarray, snps: int, indiv: int, part: int, nparts: int, 
         _check(rc, "mb200_grm_partition")
     lr = np.arange(lrows)
     return ((lr // 128) * nparts + part) * 128 + lr % 128, panel
+
+
+def bed_shape(file: str):
+    """(n_snps, n_indiv) of a PLINK .bed/.bim/.fam triple after read_bed's checks
+    (read_plink.jl:161-195); raises MiraculixError like read_bed's error() calls.  No GPU needed."""
+    s, n = C.c_long(0), C.c_long(0)
+    _check(load_library().mb200_bed_shape(file.encode(), C.byref(s), C.byref(n)), "mb200_bed_shape")
+    return s.value, n.value
+
+
+def read_bed_compressed(file: str, max_ncol: int):
+    """read_bed(file, calc_freq=true) + transpose_genotype_matrix + init_compressed in one call:
+    the file is streamed to the GPU and repacked there.  Returns (handle, freq, n_snps, n_indiv)."""
+    h, s, n = C.c_void_p(None), C.c_long(0), C.c_long(0)
+    _check(load_library().mb200_read_bed(file.encode(), max_ncol, C.byref(h), C.byref(s), C.byref(n)),
+           "mb200_read_bed")
+    return h, get_compressed_freq(h, s.value), s.value, n.value
 
 
 def cg_solve(handle: C.c_void_p, b: np.ndarray, x0: np.ndarray, lam: float = 0.0,

@@ -112,7 +112,7 @@ Handle *as_handle(void *p) {
   return h;
 }
 
-static void destroy_handle(Handle *h) {
+void destroy_handle(Handle *h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
@@ -141,7 +141,7 @@ static void destroy_handle(Handle *h) {
 }
 
 // Allocate everything a handle owns (device layout + per-call scratch); no repack yet.
-static int create_handle(long snps, long indiv, int max_n, Handle **out) {
+int create_handle(long snps, long indiv, int max_n, Handle **out) {
   *out = nullptr;
   if (snps <= 0 || indiv <= 0) return fail(-2, __func__, __LINE__, "snps=%ld indiv=%ld", snps, indiv);
   if (max_n < 1) max_n = 1;
