@@ -71,6 +71,15 @@ void get_compressed_freq(void *compressed, double *f);
 int snp_multiply_gpu(unsigned char *snp_matrix, int snps, int indiv, double *ans,
                      bool is_plink_format);
 
+/* replaces src/cuda/solve_cuda.cu:947-951 (-> dense_solve :69-278), declared in
+ * src/cuda/solve_cuda.h:84-86 and bound by src/bindings/Julia/solve.jl:172-173; it follows the GRM
+ * in examples/gblup/calculate_gblup.jl.  Solves A X = B for symmetric positive definite A
+ * (input_size x input_size, only the lower triangle of the column-major view is read), B and X
+ * input_size x rhs_cols column-major; *logdet (optional) = log det A.  *status = 0 / 1.
+ * cuSOLVER potrf/potrs underneath (library call). */
+void potrs_solve_gpu(double *A, unsigned int input_size, double *B, unsigned int rhs_cols, double *X,
+                     double *logdet, int oversubscribe, int *status);
+
 /* ------------------------------------------------------------------------------------------
  * PART 2 -- additive entry points (not in the reference)
  * ---------------------------------------------------------------------------------------- */
@@ -176,6 +185,10 @@ int mb200_grm_partition(unsigned char *snp_matrix, int snps, int indiv, bool is_
 /* Timing of the device part of the last crossproduct call on this thread, in milliseconds:
  * [0] expand+GEMM, [1] epilogue (int32 -> fp64, symmetrise, centre), [2] executed int8 ops. */
 int mb200_crossprod_last_timing(double out[3]);
+
+/* potrs_solve_gpu on device-resident data, in place: d_A becomes its Cholesky factor, d_B the
+ * solution (so the GRM of mb200_crossprod_device can be solved without leaving the GPU). */
+int mb200_potrs_solve_device(double *d_A, long n, double *d_B, long nrhs, double *d_logdet);
 
 /* ------------------------------------------------------------------------------------------
  * PLINK .bed ingest.  Replaces read_bed (src/bindings/Julia/read_plink.jl:

@@ -68,6 +68,9 @@ SIGNATURES = {
     "mb200_grm_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_bool, C.c_int, C.c_void_p,
                                       C.c_bool, C.c_int, C.c_int, C.c_void_p]),
     "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
+    "potrs_solve_gpu": (None, [C.c_void_p, C.c_uint, C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p, C.c_int,
+                               C.POINTER(C.c_int)]),
+    "mb200_potrs_solve_device": (C.c_int, [C.c_void_p, C.c_long, C.c_void_p, C.c_long, C.c_void_p]),
     "mb200_bed_shape": (C.c_int, [C.c_char_p, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
     "mb200_read_bed": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_long),
                                  C.POINTER(C.c_long)]),
@@ -256,6 +259,25 @@ def grm_partition(x: np.ndarray, snps: int, indiv: int, part: int, nparts: int, 
         _check(rc, "mb200_grm_partition")
     lr = np.arange(lrows)
     return ((lr // 128) * nparts + part) * 128 + lr % 128, panel
+
+
+def dense_solve(M: np.ndarray, B: np.ndarray, calc_logdet: bool = False, oversubscribe: bool = False):
+    """src/bindings/Julia/solve.jl:139-180: X = M \\ B for symmetric positive definite M through
+    potrs_solve_gpu; with calc_logdet returns (X, logdet)."""
+    M = np.asfortranarray(M, dtype=np.float64)
+    B2 = np.asfortranarray(B, dtype=np.float64).reshape(M.shape[0], -1, order="F")
+    if M.shape[0] != M.shape[1]:
+        raise ValueError("M must be square")
+    X = np.zeros_like(B2, order="F")
+    logdet, status = C.c_double(0.0), C.c_int(1)
+    load_library().potrs_solve_gpu(M.ctypes.data, M.shape[0], B2.ctypes.data, B2.shape[1], X.ctypes.data,
+                                   C.cast(C.byref(logdet), C.c_void_p) if calc_logdet else None,
+                                   int(oversubscribe), C.byref(status))
+    if status.value != 0:
+        raise MiraculixError("potrs_solve_gpu failed: " +
+                             load_library().mb200_last_message().decode(errors="replace"))
+    X = X.reshape(np.shape(B), order="F")
+    return (X, logdet.value) if calc_logdet else X
 
 
 def bed_shape(file: str):
