@@ -182,8 +182,6 @@ int create_handle(long snps, long indiv, int max_n, Handle **out) {
   H_CUDA(cudaMalloc(&h->d_B, sizeof(double) * mx * max_n));
   H_CUDA(cudaMalloc(&h->d_C, sizeof(double) * mx * max_n));
   H_CUDA(cudaMalloc(&h->d_w, sizeof(double) * 8 * (max_n + 16)));
-  H_CUDA(cudaMemsetAsync(h->d_snp_major, 0, (size_t)snps * h->pitch_s, h->stream));
-  H_CUDA(cudaMemsetAsync(h->d_indiv_major, 0, (size_t)indiv * h->pitch_i, h->stream));
   H_CUDA(cudaMemsetAsync(h->d_counts, 0, sizeof(unsigned long long) * snps, h->stream));
 #undef H_CUDA
   *out = h;
@@ -193,12 +191,12 @@ int create_handle(long snps, long indiv, int max_n, Handle **out) {
 int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count);
 
 // Host bed -> device layout: stream the bed through two device staging buffers in chunks of
-// whole 256-SNP tiles and repack each chunk as it lands.
+// whole 512-SNP tiles and repack each chunk as it lands.
 static int repack_from_host(Handle *h, const uint8_t *plink) {
   const long bs = ceil_div(h->indiv, 4);
-  long rows_per_chunk = (256L << 20) / bs / 256 * 256;
-  if (rows_per_chunk < 256) rows_per_chunk = 256;
-  if (rows_per_chunk > round_up(h->snps, 256)) rows_per_chunk = round_up(h->snps, 256);
+  long rows_per_chunk = (256L << 20) / bs / 512 * 512;
+  if (rows_per_chunk < 512) rows_per_chunk = 512;
+  if (rows_per_chunk > round_up(h->snps, 512)) rows_per_chunk = round_up(h->snps, 512);
   uint8_t *stage[2] = {nullptr, nullptr};
   cudaEvent_t done[2];
   for (int i = 0; i < 2; i++) {

@@ -92,9 +92,9 @@ static int bed_inspect(const char *path, long *snps, long *indiv, long *bs) {
 // Stream the payload: pinned buffer b is filled by fread while buffer b^1 is in flight to the
 // device; staged chunk -> bed_freq_kernel + repack_chunk on the handle's stream.
 static int bed_stream(Handle *h, const char *path, long bs) {
-  long rows_per_chunk = (64L << 20) / bs / 256 * 256;  // ~64 MiB, whole 256-SNP tiles
-  if (rows_per_chunk < 256) rows_per_chunk = 256;
-  if (rows_per_chunk > round_up(h->snps, 256)) rows_per_chunk = round_up(h->snps, 256);
+  long rows_per_chunk = (64L << 20) / bs / 512 * 512;  // ~64 MiB, whole 512-SNP tiles
+  if (rows_per_chunk < 512) rows_per_chunk = 512;
+  if (rows_per_chunk > round_up(h->snps, 512)) rows_per_chunk = round_up(h->snps, 512);
   const size_t chunk_bytes = (size_t)rows_per_chunk * bs;
   uint8_t *host[2] = {nullptr, nullptr}, *dev[2] = {nullptr, nullptr};
   cudaEvent_t done[2] = {nullptr, nullptr};

@@ -39,6 +39,7 @@ struct Handle {
   long pitch_i = 0;  // bytes per indiv row (indiv-major:[indiv][pitch_i], K = snps)
   uint8_t *d_snp_major = nullptr;
   uint8_t *d_indiv_major = nullptr;
+  bool zeroed = false;  // layouts memset to 0 (only the generic repack kernel needs it, repack.cu)
   double *d_f = nullptr;                   // allele frequencies (caller-supplied), length snps
   unsigned long long *d_counts = nullptr;  // allele counts per SNP from the repack
   std::vector<double> h_f;                 // host copy for get_compressed_freq

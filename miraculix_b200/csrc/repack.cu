@@ -9,6 +9,7 @@
 // accumulates the per-SNP allele counts.
 //
 // HBM-bound: algorithmic bytes = snps*ceil(indiv/4) read + snps*pitch_s + indiv*pitch_i written.
+#include <stdlib.h>
 #include "common.cuh"
 #include "handle.h"
 
@@ -92,8 +93,170 @@ repack_kernel(const uint8_t *__restrict__ plink, long s_begin, long s_count, lon
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fast path (bed rows are whole, 4-byte aligned words: ceil(indiv/4) % 4 == 0): 512 SNP x 512
+// individual tiles, so every global access is a full 128-byte line per row -- in (bed row
+// segment), out SNP-major (same segment, recoded) and out individual-major (32 words = 512 SNPs of
+// one individual).  The tile is transposed IN PLACE in shared memory as 32 x 32 blocks of 16 x 16
+// 2-bit fields: a thread loads block (q, cw) (16 words: SNP rows 16q.., word column cw) into
+// registers, transposes it with 4 rounds of delta swaps between the words, and stores it as block
+// (cw, q).  Smem layout S[k][q][w] (row = 16 q + k, pitch 33 words) makes the block loads (lanes =
+// cw), the swapped stores (lanes = cw -> stride 33) and the row-wise copy-out conflict-free.
+// ---------------------------------------------------------------------------------------------
+constexpr int RF_TILE = 512;
+constexpr int RF_THREADS = 512;
+constexpr int RF_QP = 33;                       // words per (k, q) row of S
+constexpr int RF_KP = 32 * RF_QP + 1;           // words per k plane (+1: 4 rows of a warp hit 4 bank groups)
+constexpr int RF_SMEM = 16 * RF_KP * 4;         // 67648 bytes
+
+__device__ __forceinline__ void transpose16x16_2bit(uint32_t (&a)[16]) {
+#pragma unroll
+  for (int k = 0; k < 8; k++) {   // fields 8..15 of word k <-> fields 0..7 of word k + 8
+    const uint32_t t = ((a[k] >> 16) ^ a[k + 8]) & 0x0000FFFFu;
+    a[k + 8] ^= t; a[k] ^= t << 16;
+  }
+#pragma unroll
+  for (int k = 0; k < 16; k++)
+    if (!(k & 4)) { const uint32_t t = ((a[k] >> 8) ^ a[k + 4]) & 0x00FF00FFu; a[k + 4] ^= t; a[k] ^= t << 8; }
+#pragma unroll
+  for (int k = 0; k < 16; k++)
+    if (!(k & 2)) { const uint32_t t = ((a[k] >> 4) ^ a[k + 2]) & 0x0F0F0F0Fu; a[k + 2] ^= t; a[k] ^= t << 4; }
+#pragma unroll
+  for (int k = 0; k < 16; k++)
+    if (!(k & 1)) { const uint32_t t = ((a[k] >> 2) ^ a[k + 1]) & 0x33333333u; a[k + 1] ^= t; a[k] ^= t << 2; }
+}
+
+template <int VW> struct RfVec;
+template <> struct RfVec<1> { typedef uint32_t T; };
+template <> struct RfVec<2> { typedef uint2 T; };
+template <> struct RfVec<4> { typedef uint4 T; };
+
+// VW = words per thread in phase 1 (1, 2 or 4: what the alignment of the bed rows allows)
+template <int VW>
+__global__ void __launch_bounds__(RF_THREADS, 3)
+repack_fast_kernel(const uint32_t *__restrict__ plink, long s_begin, long s_count, long snps,
+                   long indiv, long wpr /* words per bed row */, uint8_t *__restrict__ snp_major,
+                   long pitch_s, uint8_t *__restrict__ indiv_major, long pitch_i,
+                   unsigned long long *__restrict__ counts) {
+  extern __shared__ uint32_t S[];
+  typedef typename RfVec<VW>::T Vec;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const long w0 = (long)blockIdx.x * 32;                  // first word column (16 individuals each)
+  const long sl0 = (long)blockIdx.y * RF_TILE;            // first SNP of the tile, chunk-local
+  const bool edge = 16 * (w0 + 32) > indiv;               // tile holds the ragged end of the rows
+
+  // phase 1: 32 / VW lanes per SNP row; read, recode, count, write SNP-major, stage plain in smem
+  {
+    constexpr int LPR = 32 / VW;                          // lanes per row
+    constexpr int RPI = RF_THREADS / LPR;                 // rows per iteration
+    const int wl = (tid % LPR) * VW;                      // first word of this thread in the segment
+    const long gw = w0 + wl;
+#pragma unroll 2
+    for (int r = tid / LPR; r < RF_TILE; r += RPI) {
+      const long sl = sl0 + r;
+      uint32_t v[VW];
+#pragma unroll
+      for (int j = 0; j < VW; j++) v[j] = 0;
+      int cnt = 0;
+      const bool in_row = sl < s_count && gw < wpr;       // wpr % VW == 0: the vector is whole
+      if (in_row) {
+        const Vec raw = __ldg(reinterpret_cast<const Vec *>(plink + sl * wpr + gw));
+        const uint32_t *rw = reinterpret_cast<const uint32_t *>(&raw);
+        uint32_t o[VW];
+#pragma unroll
+        for (int j = 0; j < VW; j++) {
+          v[j] = plink_to_value_word(rw[j]);
+          if (edge) {
+            const long keep = indiv - 16 * (gw + j);      // valid fields in this word
+            if (keep < 16) v[j] = keep > 0 ? v[j] & ((1u << (2 * keep)) - 1u) : 0u;
+          }
+          cnt += __popc(v[j]) + __popc(v[j] & 0xAAAAAAAAu);   // sum of 2-bit values
+          o[j] = interleave_word(v[j]);
+        }
+        *reinterpret_cast<Vec *>(snp_major + (s_begin + sl) * pitch_s + 4 * gw) =
+            *reinterpret_cast<const Vec *>(o);
+      } else if (sl < s_count) {                          // row padding up to the 128-byte pitch
+        *reinterpret_cast<Vec *>(snp_major + (s_begin + sl) * pitch_s + 4 * gw) =
+            *reinterpret_cast<const Vec *>(v);
+      }
+      uint32_t *dst = S + (r & 15) * RF_KP + (r >> 4) * RF_QP + wl;
+#pragma unroll
+      for (int j = 0; j < VW; j++) dst[j] = v[j];
+#pragma unroll
+      for (int o2 = LPR / 2; o2; o2 >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o2);
+      if ((tid % LPR) == 0 && cnt) atomicAdd(&counts[s_begin + sl], (unsigned long long)cnt);
+    }
+  }
+  __syncthreads();
+
+  // phase 2: in-place transpose, two blocks per thread (block id = q * 32 + cw, lanes = cw).
+  // SNP row k of a block is loaded into register 4 (k % 4) + k / 4, so the transposed word comes
+  // out with its 16 SNP fields already in the interleaved order of the device layout.
+  uint32_t a0[16], a1[16];
+  const int q0b = tid >> 5, q1b = q0b + 16, cw = lane;
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    a0[4 * (k & 3) + (k >> 2)] = S[k * RF_KP + q0b * RF_QP + cw];
+    a1[4 * (k & 3) + (k >> 2)] = S[k * RF_KP + q1b * RF_QP + cw];
+  }
+  __syncthreads();
+  transpose16x16_2bit(a0);
+  transpose16x16_2bit(a1);
+#pragma unroll
+  for (int il = 0; il < 16; il++) {   // word il = individual 16 cw + il, fields = SNPs 16 q ..
+    S[il * RF_KP + cw * RF_QP + q0b] = a0[il];
+    S[il * RF_KP + cw * RF_QP + q1b] = a1[il];
+  }
+  __syncthreads();
+
+  // phase 3: 8 lanes per individual row of the tile (4 words = 16 bytes each), 128 B per row
+  const long gq0 = (s_begin + sl0) >> 4;                  // s_begin, sl0 are multiples of 512
+  const int wl = (tid & 7) * 4;
+  const long gq = gq0 + wl;
+  const long qwords = pitch_i >> 2;                       // whole pitch: SNP rows past the end are 0
+#pragma unroll 2
+  for (int r = tid >> 3; r < RF_TILE; r += RF_THREADS / 8) {
+    const long i = 16 * w0 + r;
+    if (i < indiv && gq < qwords) {                       // the kernel writes the row padding too
+      const uint32_t *src = S + (r & 15) * RF_KP + (r >> 4) * RF_QP + wl;
+      *reinterpret_cast<uint4 *>(indiv_major + i * pitch_i + 4 * gq) =
+          make_uint4(src[0], src[1], src[2], src[3]);
+    }
+  }
+}
+
 int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count) {
   const long bs = ceil_div(h->indiv, 4);
+  static int use_fast = -1;
+  if (use_fast < 0) {
+    const char *e = getenv("MB200_REPACK_FAST");
+    use_fast = e ? atoi(e) : 1;
+    cudaFuncSetAttribute(repack_fast_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
+    cudaFuncSetAttribute(repack_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
+    cudaFuncSetAttribute(repack_fast_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
+  }
+  if (use_fast && bs % 4 == 0 && (reinterpret_cast<uintptr_t>(d_chunk) & 3) == 0 &&
+      s_begin % RF_TILE == 0) {
+    dim3 grid((unsigned)ceil_div(bs / 4, 32), (unsigned)ceil_div(s_count, RF_TILE));
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(d_chunk);
+    const uintptr_t al = reinterpret_cast<uintptr_t>(d_chunk);
+#define RF_LAUNCH(VW)                                                                          \
+  repack_fast_kernel<VW><<<grid, RF_THREADS, RF_SMEM, h->stream>>>(                              \
+      src, s_begin, s_count, h->snps, h->indiv, bs / 4, h->d_snp_major, h->pitch_s,             \
+      h->d_indiv_major, h->pitch_i, h->d_counts)
+    if (bs % 16 == 0 && al % 16 == 0) RF_LAUNCH(4);
+    else if (bs % 8 == 0 && al % 8 == 0) RF_LAUNCH(2);
+    else RF_LAUNCH(1);
+#undef RF_LAUNCH
+    count_launch();
+    MB_LAUNCH_CHECK();
+    return 0;
+  }
+  if (!h->zeroed) {  // the generic kernel relies on zero-initialised padding
+    MB_CUDA(cudaMemsetAsync(h->d_snp_major, 0, (size_t)h->snps * h->pitch_s, h->stream));
+    MB_CUDA(cudaMemsetAsync(h->d_indiv_major, 0, (size_t)h->indiv * h->pitch_i, h->stream));
+    h->zeroed = true;
+  }
   dim3 grid((unsigned)ceil_div(h->indiv, RP_TILE), (unsigned)ceil_div(s_count, RP_TILE));
   repack_kernel<<<grid, 256, 0, h->stream>>>(d_chunk, s_begin, s_count, h->snps, h->indiv, bs,
                                              h->d_snp_major, h->pitch_s, h->d_indiv_major,
@@ -106,7 +269,7 @@ int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count) 
 int repack_from_device(Handle *h, const uint8_t *d_plink) {
   // grid.y limit 65535 tiles = 16.7M SNPs per launch; chunk to stay below
   const long bs = ceil_div(h->indiv, 4);
-  const long max_rows = 65535L * RP_TILE;
+  const long max_rows = 65534L * RP_TILE;  // multiple of 512: keeps the fast path's tile alignment
   for (long s = 0; s < h->snps; s += max_rows) {
     long cnt = h->snps - s < max_rows ? h->snps - s : max_rows;
     MB_CHECK(repack_chunk(h, d_plink + s * bs, s, cnt));

@@ -32,7 +32,11 @@ def _centered(gpu_lib):
 
 @pytest.mark.parametrize("snps,indiv,missing", [(1, 1, 0.0), (5, 3, 0.0), (256, 256, 0.0),
                                                 (1003, 203, 0.02), (513, 1025, 0.05),
-                                                (10000, 1000, 0.0), (300, 4099, 0.01)])
+                                                (10000, 1000, 0.0), (300, 4099, 0.01),
+                                                # whole-word bed rows: the 512 x 512 in-place
+                                                # transpose kernel, ragged in both directions
+                                                (1003, 208, 0.02), (5000, 1037, 0.01),
+                                                (700, 8208, 0.0), (1537, 16, 0.05), (512, 512, 0.0)])
 def test_repack_bit_exact(gpu_lib, snps, indiv, missing):
     from miraculix_b200 import api
     plink, Z, f = simulate.simulate(snps, indiv, seed=snps * 7 + indiv, missing=missing)
