@@ -16,11 +16,12 @@ namespace mb200 {
 
 struct TileCoord;
 int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
-                    cudaStream_t stream);
+                    cudaStream_t stream, int split_kblocks, int grid_max, int *num_tail,
+                    int *real_tiles);
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream, const CpFinish *finish);
+                        cudaStream_t stream, const CpFinish *finish, int num_tail);
 
 static int upload_lut() {
   uint8_t table[256];
@@ -67,7 +68,10 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
   if (need_c32) MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
-  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream));
+  int real_tiles = 0;
+  int num_tail = 0;  // single slab: the last partial round of tiles is cut along K (crossprod_tc.cu)
+  const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
+  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   // GRM: the row sums m = M 1 come exactly from the input, m = X (X^T 1) (64-bit integers), so
@@ -105,8 +109,8 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     MB_LAUNCH_CHECK();
     if (tc) {
       MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
-                                   sms, stream, slab == nslabs - 1 ? &fin : nullptr));
-      executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
+                                   sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail));
+      executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
     } else {
       const unsigned g = (unsigned)(rows_pad / 64);
       crossprod_simt_kernel<<<dim3(g, g), 256, 0, stream>>>(X8, kpad, C32, rows_pad, slab > 0);
@@ -202,7 +206,10 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   if (nslabs > 1)  // int32 partials only exist when K needs several slabs
     MB_CUDA(cudaMallocAsync(&C32, (size_t)local_rows * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
-  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream));
+  int real_tiles = 0;
+  int num_tail = 0;
+  const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
+  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   if (mode == 1) {
@@ -240,8 +247,8 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     count_launch();
     MB_LAUNCH_CHECK();
     MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
-                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr));
-    executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)num_tiles;
+                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail));
+    executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
   }
   MB_CUDA(cudaEventRecord(e2, stream));
 

@@ -40,6 +40,10 @@ struct TileCoord {
   int mi, nj;  // operand tiles: rows mi*128.. of X against rows nj*256.. of X
   int mo;      // output row tile: C32 row = mo*128 + r (== mi unless the output is a compact
                // panel of one partition's row tiles, crossprod.cu)
+  // Balanced tail: the tiles of the last, partial round of the static round-robin are cut along K
+  // into pieces [kb0, kb1) dealt one per CTA; a piece adds its int32 partial into scratch tile
+  // `slot` (red.global.add) and tail_finish_kernel applies the epilogue.  Whole tiles: kb1 = -1.
+  int kb0, kb1, slot;
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -82,7 +86,8 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint32_t phase = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const TileCoord tc = tiles[t];
-      for (int kb = 0; kb < num_kblocks; kb++) {
+      const int kb1 = tc.kb1 < 0 ? num_kblocks : tc.kb1;
+      for (int kb = tc.kb0; kb < kb1; kb++) {
         mbar_wait_warp(&empty[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t *sa = smem + stage * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
@@ -105,7 +110,8 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_wait_warp(&tempty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * TC_BN;
-      for (int kb = 0; kb < num_kblocks; kb++) {
+      const int kb0 = tiles[t].kb0, kb1 = tiles[t].kb1 < 0 ? num_kblocks : tiles[t].kb1;
+      for (int kb = kb0; kb < kb1; kb++) {
         mbar_wait_warp(&full[stage], phase);
         tc_fence_after();
         if (elect_one()) {
@@ -114,9 +120,9 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint64_t bdesc = make_desc_k_sw128(sa + TC_A_BYTES);
 #pragma unroll
           for (int k4 = 0; k4 < TC_BK / 32; k4++)  // +32 bytes along K = +2 in the >>4 address field
-            mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb | k4) ? 1u : 0u);
+            mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb > kb0 || k4) ? 1u : 0u);
           tc_commit(&empty[stage]);
-          if (kb == num_kblocks - 1) tc_commit(&tfull[acc]);
+          if (kb == kb1 - 1) tc_commit(&tfull[acc]);
         }
         __syncwarp();
         if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
@@ -148,6 +154,12 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr + c * 32, r);
         tmem_ld_wait();
+        if (tc.slot >= 0) {  // K piece of a tail tile: int32 partial into the scratch tile
+          int *dst = fin.tail + ((long)tc.slot * TC_BM + quad * 32 + lane) * TC_BN + c * 32;
+#pragma unroll
+          for (int q = 0; q < 32; q++) atomicAdd(dst + q, (int)r[q]);
+          continue;
+        }
         if (fin.kind == 0) {
           int4 *dst = reinterpret_cast<int4 *>(crow + c * 32);
 #pragma unroll
@@ -265,18 +277,72 @@ int make_tmap_u8_2d(CUtensorMap *map, const void *base, long row_bytes, long row
 // ~148 tiles in flight share operand panels in L2.
 // part/nparts: row tile mi belongs to partition mi % nparts and is written to the compact output
 // row tile mi / nparts (2-D output-tile partition over GPUs: no communication, cyclic = balanced).
+// Epilogue of the K-split tail tiles: scratch int32 tile -> the same finish as the GEMM epilogue.
+__global__ void __launch_bounds__(256)
+tail_finish_kernel(const TileCoord *__restrict__ tail_tiles, const int *__restrict__ scratch,
+                   const CpFinish fin) {
+  const TileCoord tc = tail_tiles[blockIdx.x];
+  const double alpha = -1.0 / (double)fin.n;
+  const double shift = fin.affine ? fin.scal[0] / ((double)fin.n * (double)fin.n) : 0.0;
+  const double rc = fin.affine && fin.do_scale ? 1.0 / fin.scal[1] : 1.0;
+  const int *src = scratch + (long)blockIdx.x * TC_BM * TC_BN;
+  for (int e = threadIdx.x; e < TC_BM * TC_BN; e += 256) {
+    // kind 1 stores column-major (consecutive threads = consecutive rows), kind 2 row-major
+    const int r = fin.kind == 1 ? e % TC_BM : e / TC_BN, c = fin.kind == 1 ? e / TC_BM : e % TC_BN;
+    const long lrow = (long)tc.mo * TC_BM + r;
+    const long gi = fin.kind == 2 ? ((long)tc.mo * fin.nparts + fin.part) * TC_BM + r : lrow;
+    const long j = (long)tc.nj * TC_BN + c;
+    if (gi >= fin.n || j >= fin.n) continue;
+    const double v = (double)src[r * TC_BN + c];
+    const double mi = fin.affine ? fin.m[gi] : 0.0, mj = fin.affine ? fin.m[j] : 0.0;
+    if (fin.kind == 1) {
+      if (gi > j) continue;
+      fin.out[gi + j * fin.n] = fin.affine ? cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale) : v;
+      fin.out[j + gi * fin.n] = fin.affine ? cp_affine(v, mj, mi, alpha, shift, rc, fin.do_scale) : v;
+    } else {
+      fin.out[lrow * fin.n + j] = fin.affine ? cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale) : v;
+    }
+  }
+}
+
+// split_kblocks > 0: K blocks per tile of a single-slab product whose last partial round may be
+// cut into K pieces (see TileCoord); *num_tail = tiles cut, their coordinates follow the work list
+// at (*d_tiles)[*num_tiles ...].
 int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
-                    cudaStream_t stream) {
+                    cudaStream_t stream, int split_kblocks, int grid_max, int *num_tail,
+                    int *real_tiles) {
   const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
   std::vector<TileCoord> v;
   for (int sn = 0; sn < Nt; sn += 8)
     for (int sm = 0; sm < Mt; sm += 16 * nparts)
       for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
         for (int mi = sm + part; mi < sm + 16 * nparts && mi < Mt; mi += nparts)
-          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts});
-  const int real_tiles = (int)v.size();
-  if (v.empty()) v.push_back({0, 0, 0});  // keep the allocation non-empty; the launch is skipped
-  *num_tiles = real_tiles;
+          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts, 0, -1, -1});
+  int ntail = 0;
+  const int T = (int)v.size();
+  if (split_kblocks > 0 && grid_max > 0 && T > grid_max) {
+    const int rem = T % grid_max;
+    const int P = rem ? grid_max / rem : 0;              // K pieces per tail tile
+    if (rem && P >= 2 && split_kblocks >= 4 * P) {       // worth it: <= half a round, pieces >= 4 blocks
+      std::vector<TileCoord> tail(v.end() - rem, v.end());
+      v.resize(T - rem);
+      for (int p = 0; p < P; p++)                        // piece-major: the pieces of one tile
+        for (int t = 0; t < rem; t++) {                  // run on different CTAs at the same time
+          TileCoord c = tail[t];
+          c.kb0 = (int)((long)split_kblocks * p / P);
+          c.kb1 = (int)((long)split_kblocks * (p + 1) / P);
+          c.slot = t;
+          v.push_back(c);
+        }
+      ntail = rem;
+      *num_tiles = (int)v.size();
+      v.insert(v.end(), tail.begin(), tail.end());
+    }
+  }
+  if (!ntail) *num_tiles = T;
+  if (num_tail) *num_tail = ntail;
+  if (real_tiles) *real_tiles = T;
+  if (v.empty()) v.push_back({0, 0, 0, 0, -1, -1});  // keep the allocation non-empty; the launch is skipped
   MB_CUDA(cudaMallocAsync(d_tiles, sizeof(TileCoord) * v.size(), stream));
   MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice,
                           stream));
@@ -287,7 +353,7 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream, const CpFinish *finish) {
+                        cudaStream_t stream, const CpFinish *finish, int num_tail) {
   MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                TC_SMEM));
   CUtensorMap ta, tb;
@@ -295,11 +361,26 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
   MB_CHECK(make_tmap_u8_2d(&tb, X8, kcols, rows_pad, pitch, TC_BK, TC_BN, 1));
   if (num_tiles <= 0) return 0;
   const int grid = num_tiles < sm_count ? num_tiles : sm_count;
+  CpFinish fin = finish ? *finish : CpFinish();
+  int *scratch = nullptr;
+  if (num_tail > 0) {
+    if (!finish || !finish->kind) return fail(-2, __func__, __LINE__, "split tail needs a finishing epilogue");
+    const size_t bytes = sizeof(int) * (size_t)num_tail * TC_BM * TC_BN;
+    MB_CUDA(cudaMallocAsync(&scratch, bytes, stream));
+    MB_CUDA(cudaMemsetAsync(scratch, 0, bytes, stream));
+    fin.tail = scratch;
+  }
   crossprod_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
                                                              (int)(kcols / TC_BK), C32, ld32,
-                                                             accumulate, finish ? *finish : CpFinish());
+                                                             accumulate, fin);
   count_launch();
   MB_LAUNCH_CHECK();
+  if (num_tail > 0) {
+    tail_finish_kernel<<<num_tail, 256, 0, stream>>>(d_tiles + num_tiles, scratch, fin);
+    count_launch();
+    MB_LAUNCH_CHECK();
+    MB_CUDA(cudaFreeAsync(scratch, stream));
+  }
   return 0;
 }
 

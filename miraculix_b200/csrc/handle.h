@@ -118,6 +118,7 @@ struct CpFinish {
   double *out = nullptr;
   const double *m = nullptr;     // row sums of the count matrix
   const double *scal = nullptr;  // [0] = sum m, [1] = 2 sum f (1 - f)
+  int *tail = nullptr;           // scratch tiles of the K-split tail (crossprod_tc.cu), set by the launcher
 };
 
 // crossprod.cu

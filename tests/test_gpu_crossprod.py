@@ -174,3 +174,25 @@ def test_grm_partition_assembles_to_full(gpu_lib, snps, indiv, nparts):
         assert seen == indiv  # every row owned exactly once
         iu = np.triu_indices(indiv)
         assert np.array_equal(got[iu], full[iu]), mode
+
+
+def test_k_split_tail_matches_unsplit(gpu_lib, monkeypatch):
+    """Shape whose upper-triangle tile count (156) leaves a partial last round on 148 SMs: those
+    tiles are cut along K into pieces (int32 partials in a scratch tile + tail_finish_kernel).
+    Counts must stay exact and the centred GRM bit-identical to the unsplit schedule; the
+    partition panels go through the same path."""
+    from miraculix_b200 import api
+    snps, indiv = 9300, 3000
+    _, Z, f = simulate.simulate(snps, indiv, seed=77)
+    x = simulate.pack_2bit(Z)
+    M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False)
+    assert np.array_equal(M, exact_counts(Z))
+    G = api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
+    rows, panel = api.grm_partition(x, snps, indiv, 1, 2, mode=1, do_scale=True, allele_freq=f)
+    monkeypatch.setenv("MB200_NO_TAIL_SPLIT", "1")
+    G0 = api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
+    rows0, panel0 = api.grm_partition(x, snps, indiv, 1, 2, mode=1, do_scale=True, allele_freq=f)
+    assert np.array_equal(G, G0)
+    assert np.array_equal(panel, panel0)
+    want = cport.grm_epilogue(exact_counts(Z), f, True)
+    assert relerr(G, want) <= TOL
