@@ -646,8 +646,25 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   if (chunks > Handle::kPipeMax) chunks = Handle::kPipeMax;
   if (chunks < 1 || (double)h->snps * n * 8.0 < options().pipe_min_bytes) chunks = 1;
   if (!pipe_in && !pipe_out) chunks = 1;
-  long per = round_up(ceil_div(h->snps, chunks), 512);
-  chunks = (int)ceil_div(h->snps, per);
+  // Chunk sizes grow 1 : 2 : 3 : ... towards the end that is NOT exposed: the exposed copy (the
+  // first upload of 'N', the last download of 'T') is the small one, every other copy hides behind
+  // a kernel that is at least as long.  Boundaries are multiples of 512 SNPs.
+  long bnd[Handle::kPipeMax + 1];
+  {
+    const long blocks = ceil_div(h->snps, 512);
+    if (chunks > blocks) chunks = (int)blocks;
+    const long tri = (long)chunks * (chunks + 1) / 2;
+    bnd[0] = 0;
+    long acc = 0;
+    for (int i = 0; i < chunks; i++) {
+      acc += trans ? chunks - i : i + 1;                     // weights 1..c ('N') or c..1 ('T')
+      long b = (blocks * acc + tri - 1) / tri * 512;
+      if (b <= bnd[i]) b = bnd[i] + 512;
+      bnd[i + 1] = b < h->snps && i + 1 < chunks ? b : h->snps;
+      if (bnd[i + 1] >= h->snps) { chunks = i + 1; break; }
+    }
+    bnd[chunks] = h->snps;
+  }
   int *h_flag = reinterpret_cast<int *>(h->h_pipe);
   *h_flag = 0;
   MB_CUDA(cudaMemsetAsync(tc_flag(h), 0, sizeof(int), h->stream));
@@ -664,7 +681,7 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   if (!trans) {
     MB_CUDA(cudaMemsetAsync(tc_amax_all(h), 0, sizeof(unsigned long long) * n, h->stream));
     for (int i = 0; i < chunks; i++) {
-      const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
+      const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
       if (pipe_in) {
         MB_CUDA(copy2d(h->d_B + s0, k, B + s0, ldb, cnt, n, cudaMemcpyHostToDevice, h->copy_stream));
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
@@ -677,7 +694,7 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
     if (adaptive) MB_CHECK(tc_check(h, dC, ldC, m, n, S, tc_amax_all(h), full.rowsum_max));
   } else {
     for (int i = 0; i < chunks; i++) {
-      const long s0 = i * per, cnt = h->snps - s0 < per ? h->snps - s0 : per;
+      const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
       const DgemmView v = sub_view(h, 1, s0, cnt);
       MB_CHECK(tc_pass(h, v, n, dB, ldB, dC + s0, ldC, S, 0, nullptr, nullptr, &first_main, ev));
       if (adaptive)
