@@ -80,6 +80,24 @@ int snp_multiply_gpu(unsigned char *snp_matrix, int snps, int indiv, double *ans
 void potrs_solve_gpu(double *A, unsigned int input_size, double *B, unsigned int rhs_cols, double *X,
                      double *logdet, int oversubscribe, int *status);
 
+/* replaces src/miraculix/5codesAPI.c:131-157 (-> sparseTGenoPlinkApi 5codesChar.cc:472-492 ->
+ * sparseTGeno haplogeno.cc:1685-1713 -> sparseTGenoPlink plinkUint.cc:303-352; CPU only in the
+ * reference), bound by src/bindings/Fortran/mod5codesapi.f90:84-100.  CSR sparse matrix
+ * (rowIdxB[nIdx+1], colIdxB, B; 0-based) times the PLINK-coded genotypes, uncentred, missing = 0:
+ *   transcompressed 'N': C[nIdx x indiv] = S[nIdx x snps]  Z^T   (rows of `plink` = SNPs)
+ *   transcompressed 'T': C[nIdx x snps ] = S[nIdx x indiv] Z     (rows of `plink_transposed`)
+ * C column-major with leading dimension Ldc; the whole Ldc x columns block is zeroed first, as
+ * the reference does.  transsparse must be 'N' (the reference aborts otherwise; so do we). */
+void sparse_times_plink(char *transsparse, char *transcompressed, char *plink, char *plink_transposed,
+                        int snps, int indiv, int nIdx, int *rowIdxB, int *colIdxB, double *B,
+                        double *C, int Ldc);
+/* replaces src/miraculix/5codesAPI.c:112-127.  In the reference this entry is a BUG() stub
+ * (vectorGenoPlinkApi 5codesChar.cc:495-519 -> plink256.cc:332); here it is the one-shot product
+ * plink2compressed + dgemm_compressed + free_compressed: f == NULL gives the raw Z product, f !=
+ * NULL the centred one.  plink_transposed is not read. */
+void dgemm_plink(char *trans, char *plink, char *plink_transposed, int snps, int indiv, double *f,
+                 int n, double *B, int Ldb, double *C, int Ldc);
+
 /* ------------------------------------------------------------------------------------------
  * PART 2 -- additive entry points (not in the reference)
  * ---------------------------------------------------------------------------------------- */

@@ -68,6 +68,10 @@ SIGNATURES = {
     "mb200_grm_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_bool, C.c_int, C.c_void_p,
                                       C.c_bool, C.c_int, C.c_int, C.c_void_p]),
     "mb200_crossprod_last_timing": (C.c_int, [C.POINTER(C.c_double * 3)]),
+    "sparse_times_plink": (None, [C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "dgemm_plink": (None, [C.c_char_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                           C.c_void_p, C.c_int, C.c_void_p, C.c_int]),
     "potrs_solve_gpu": (None, [C.c_void_p, C.c_uint, C.c_void_p, C.c_uint, C.c_void_p, C.c_void_p, C.c_int,
                                C.POINTER(C.c_int)]),
     "mb200_potrs_solve_device": (C.c_int, [C.c_void_p, C.c_long, C.c_void_p, C.c_long, C.c_void_p]),
@@ -278,6 +282,46 @@ def dense_solve(M: np.ndarray, B: np.ndarray, calc_logdet: bool = False, oversub
                              load_library().mb200_last_message().decode(errors="replace"))
     X = X.reshape(np.shape(B), order="F")
     return (X, logdet.value) if calc_logdet else X
+
+
+def sparse_times_plink(transcompressed: str, plink: np.ndarray, plink_transposed, snps: int,
+                       indiv: int, row_idx: np.ndarray, col_idx: np.ndarray, values: np.ndarray,
+                       ldc: int | None = None) -> np.ndarray:
+    """c_sparse_times_plink of mod5codesapi.f90:84-100: CSR (0-based) times PLINK genotypes.
+    'N': plink (snps, ceil(indiv/4)) -> (nIdx, indiv); 'T': plink_transposed (indiv, ceil(snps/4))
+    -> (nIdx, snps).  Returns the (ldc, columns) column-major array."""
+    t = transcompressed in "TtYy"
+    row_idx = np.ascontiguousarray(row_idx, dtype=np.int32)
+    col_idx = np.ascontiguousarray(col_idx, dtype=np.int32)
+    values = np.ascontiguousarray(values, dtype=np.float64)
+    n_idx = len(row_idx) - 1
+    ldc = n_idx if ldc is None else ldc
+    code = np.ascontiguousarray(plink_transposed if t else plink, dtype=np.uint8)
+    width = snps if t else indiv
+    out = np.zeros((ldc, width), dtype=np.float64, order="F")
+    lib = load_library()
+    lib.sparse_times_plink(b"N", transcompressed.encode()[:1], code.ctypes.data, code.ctypes.data, snps,
+                           indiv, n_idx, row_idx.ctypes.data, col_idx.ctypes.data, values.ctypes.data,
+                           out.ctypes.data, ldc)
+    _check(lib.mb200_last_status(), "sparse_times_plink")
+    return out
+
+
+def dgemm_plink(trans: str, plink: np.ndarray, snps: int, indiv: int, B: np.ndarray,
+                freq: np.ndarray | None = None) -> np.ndarray:
+    """One-shot product straight from the bed payload (5codesAPI.c:112-127)."""
+    t = trans in "TtYy"
+    plink = np.ascontiguousarray(plink, dtype=np.uint8)
+    B = np.asfortranarray(B, dtype=np.float64)
+    k, n = B.shape
+    m = snps if t else indiv
+    out = np.zeros((m, n), dtype=np.float64, order="F")
+    f = np.ascontiguousarray(freq, dtype=np.float64) if freq is not None else None
+    lib = load_library()
+    lib.dgemm_plink(trans.encode()[:1], plink.ctypes.data, plink.ctypes.data, snps, indiv,
+                    f.ctypes.data if f is not None else None, n, B.ctypes.data, k, out.ctypes.data, m)
+    _check(lib.mb200_last_status(), "dgemm_plink")
+    return out
 
 
 def bed_shape(file: str):

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmiraculix_b200.so")
-SOURCES = ["abi.cu", "repack.cu", "dgemm.cu", "dgemm_tc.cu", "crossprod.cu", "crossprod_tc.cu", "solver.cu", "bedfile.cu", "dense_solve.cu"]
+SOURCES = ["abi.cu", "repack.cu", "dgemm.cu", "dgemm_tc.cu", "crossprod.cu", "crossprod_tc.cu", "solver.cu", "bedfile.cu", "dense_solve.cu", "sparse_plink.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
