@@ -50,6 +50,10 @@ def parse_args():
     ap.add_argument("--pcg-iters", type=int, default=20)
     ap.add_argument("--grm-snps", type=int, default=50_000)
     ap.add_argument("--grm-indiv", type=int, default=10_000)
+    ap.add_argument("--grm-full", type=int, default=-1,
+                    help="configs[4] (1M SNPs x 100k individuals GRM over the GPUs): 1 on, 0 off, -1 = on at 8 GPUs")
+    ap.add_argument("--grm-full-snps", type=int, default=1_000_000)
+    ap.add_argument("--grm-full-indiv", type=int, default=100_000)
     ap.add_argument("--cpu-snps", type=int, default=100_000)
     ap.add_argument("--cpu-indiv", type=int, default=10_000)
     return ap.parse_args()
@@ -286,7 +290,12 @@ def run_ours(args):
         pcg = run_pcg(args, lib, api, dev, rank, world)
     grm_part = None
     if not args.no_grm and world > 1:
-        grm_part = run_grm_partition(args, lib, api, dev, rank, world)
+        grm_part = run_grm_partition(args, lib, api, dev, rank, world, args.grm_snps, args.grm_indiv,
+                                     "BASELINE configs[1]")
+    grm_full = None
+    if not args.no_grm and world > 1 and (args.grm_full == 1 or (args.grm_full < 0 and world == 8)):
+        grm_full = run_grm_partition(args, lib, api, dev, rank, world, args.grm_full_snps,
+                                     args.grm_full_indiv, "BASELINE configs[4]", reps=2, warm=1)
 
     units_step = 2.0 * snps * indiv * ncol
     value = units_step * args.steps / (total_ms * 1e-3)
@@ -358,6 +367,8 @@ def run_ours(args):
         line["grm"] = run_grm(args, lib, api, dev)
     if grm_part is not None:
         line["grm"] = grm_part
+    if grm_full is not None:
+        line["grm_full"] = grm_full
     if not args.no_cpu:
         try:
             line["cpu_baseline"] = run_cpu_baseline(args)
@@ -430,20 +441,23 @@ def run_pcg(args, lib, api, dev, rank, world):
                                  "(ncol = 1: 't' then 'n'), per GPU"}}
 
 
-def run_grm_partition(args, lib, api, dev, rank, world):
+def run_grm_partition(args, lib, api, dev, rank, world, snps, indiv, label, reps=None, warm=None):
     """configs[1]/[4] over N GPUs: 2-D output-tile partition, NO communication -- every rank holds
     the packed matrix and computes the 128-row tiles t with t % N == rank of the centred GRM
     (mb200_crossprod_partition_device).  Time = max over ranks of the device time."""
     import torch
     import torch.distributed as dist
-    snps, indiv = args.grm_snps, args.grm_indiv
+    warm = args.warmup if warm is None else warm
+    reps = warm + (max(3, min(args.steps, 10)) if reps is None else reps)
     bs = (indiv + 3) // 4
+    torch.cuda.empty_cache()
     bed = torch.empty(snps * bs, dtype=torch.uint8, device=dev)
     api._check(lib.mb200_simulate_plink_device(C.c_void_p(bed.data_ptr()), snps, indiv, 4242), "simulate")
     h = C.c_void_p(None)
     api._check(lib.mb200_plink2compressed_device(C.c_void_p(bed.data_ptr()), snps, indiv, None, 1,
                                                  C.byref(h)), "plink2compressed_device")
     del bed
+    torch.cuda.empty_cache()  # the library allocates from the driver's pool, not torch's cache
     lay = api.get_layout(h)
     kcols = lay.pitch_indiv_major * 4
     f = torch.zeros(kcols, dtype=torch.float64, device=dev)
@@ -452,19 +466,20 @@ def run_grm_partition(args, lib, api, dev, rank, world):
     lrows = lib.mb200_crossprod_partition_rows(indiv, rank, world)
     panel = torch.empty(max(1, lrows) * indiv, dtype=torch.float64, device=dev)
     gemm, epi, ops = [], [], 0.0
-    reps = args.warmup + max(3, min(args.steps, 10))
     for it in range(reps):
         dist.barrier()
         api._check(lib.mb200_crossprod_partition_device(C.c_void_p(lay.d_indiv_major), kcols, indiv, 0, 1,
                                                         C.c_void_p(f.data_ptr()), 1, rank, world,
                                                         C.c_void_p(panel.data_ptr())), "crossprod_partition")
         t = api.crossprod_last_timing()
-        if it >= args.warmup:
+        if it >= warm:
             gemm.append(t["gemm_ms"])
             epi.append(t["epilogue_ms"])
             ops = t["executed_ops"]
     torch.cuda.synchronize()
     lib.free_compressed(C.byref(h))
+    del panel
+    torch.cuda.empty_cache()
     v = torch.tensor([statistics.mean(gemm), statistics.mean(epi), ops], dtype=torch.float64, device=dev)
     vmax = v.clone()
     dist.all_reduce(vmax, op=dist.ReduceOp.MAX)
@@ -475,7 +490,7 @@ def run_grm_partition(args, lib, api, dev, rank, world):
     tot = gm + ep
     alg_ops = 2.0 * indiv * indiv * snps
     int8_peak = 4500.0
-    return {"workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals (BASELINE configs[1]), "
+    return {"workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals ({label}), "
                         f"2-D output-tile partition over {world} GPUs, no communication",
             "metric": "GRM crossproduct int8 TOPS", "value": alg_ops / (tot * 1e-3) / 1e12,
             "unit": "TOPS (2*indiv^2*snps / t, full-matrix count)", "ms": tot,

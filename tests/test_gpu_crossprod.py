@@ -176,6 +176,32 @@ def test_grm_partition_assembles_to_full(gpu_lib, snps, indiv, nparts):
         assert np.array_equal(got[iu], full[iu]), mode
 
 
+def test_grm_partition_with_k_slabs(gpu_lib, monkeypatch):
+    """The configs[4] schedule (1M SNPs: the int8 expansion does not fit, K goes in slabs with int32
+    partials per partition, the fused epilogue runs on the last slab) at test size: panels of a
+    slabbed run are bit-identical to the single-slab panels, counts and centred GRM."""
+    from miraculix_b200 import api
+    snps, indiv, nparts = 4100, 900, 3
+    _, Z, f = simulate.simulate(snps, indiv, seed=91)
+    x = simulate.pack_2bit(Z)
+    for mode in (0, 1):
+        one = [api.grm_partition(x, snps, indiv, p, nparts, mode=mode, do_scale=True, allele_freq=f)
+               for p in range(nparts)]
+        monkeypatch.setenv("MB200_SLAB_GB", "0.0005")
+        try:
+            many = [api.grm_partition(x, snps, indiv, p, nparts, mode=mode, do_scale=True,
+                                      allele_freq=f) for p in range(nparts)]
+        finally:
+            monkeypatch.delenv("MB200_SLAB_GB")
+        for (r1, p1), (r2, p2) in zip(one, many):
+            assert np.array_equal(r1, r2)
+            assert np.array_equal(p1, p2), mode
+    # and against the oracle through the first partition's first row tile
+    rows, panel = many[0]
+    want = cport.grm_epilogue(exact_counts(Z), f, True)
+    assert relerr(panel[:128, :], want[rows[:128], :] * (np.arange(indiv)[None, :] >= 0)) <= TOL
+
+
 def test_k_split_tail_matches_unsplit(gpu_lib, monkeypatch):
     """Shape whose upper-triangle tile count (156) leaves a partial last round on 148 SMs: those
     tiles are cut along K into pieces (int32 partials in a scratch tile + tail_finish_kernel).
