@@ -115,8 +115,9 @@ unsigned long long mb200_kernel_launches(void);
 int mb200_set_dgemm_mode(int mode, int slices);
 /* Host-pointer dgemm_compressed overlaps the PCIe copies of the snps x n panel (B for 'N', C for
  * 'T') with the kernels by cutting the SNP axis into `chunks` pieces (default 4, at most 16;
- * boundaries multiples of 512 SNPs) whenever that panel holds at least min_bytes (default 4e6;
- * negative = keep).  Results do not depend on the chunking beyond fp64 summation order. */
+ * boundaries multiples of 512 SNPs), fewer when a chunk would hold less than min_bytes of that
+ * panel (default 1e7: a 10 MB panel is not cut at all; 0 = always `chunks`; negative = keep).
+ * Results do not depend on the chunking beyond fp64 summation order. */
 int mb200_set_pipeline(int chunks, double min_bytes);
 /* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct (default). */
 int mb200_set_crossprod_mode(int mode);

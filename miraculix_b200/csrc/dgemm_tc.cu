@@ -644,7 +644,13 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   // chunks of the SNP axis: only worth it when the big panel takes a while on PCIe
   int chunks = options().pipe_chunks;
   if (chunks > Handle::kPipeMax) chunks = Handle::kPipeMax;
-  if (chunks < 1 || (double)h->snps * n * 8.0 < options().pipe_min_bytes) chunks = 1;
+  // at least pipe_min_bytes of panel per chunk: a chunk costs ~50 us of small kernels and tails,
+  // which a PCIe copy shorter than ~0.2 ms cannot win back (measured at the 8-GPU shard size)
+  if (options().pipe_min_bytes > 0) {
+    const double per = (double)h->snps * n * 8.0 / options().pipe_min_bytes;
+    if (per < chunks) chunks = (int)per;
+  }
+  if (chunks < 1) chunks = 1;
   if (!pipe_in && !pipe_out) chunks = 1;
   // Chunk sizes grow 1 : 2 : 3 : ... towards the end that is NOT exposed: the exposed copy (the
   // first upload of 'N', the last download of 'T') is the small one, every other copy hides behind

@@ -18,7 +18,7 @@ struct Options {
   int dgemm_slices = 0;    // 8-bit digits per column of B in mode 1; 0 = adaptive (6, verified, else 8)
   int crossprod_mode = 1;  // 0 dp4a SIMT, 1 tcgen05
   int pipe_chunks = 4;             // SNP chunks of the host-pointer dgemm_compressed pipeline
-  double pipe_min_bytes = 4.0e6;   // ... used when the snps x n panel is at least this large
+  double pipe_min_bytes = 1.0e7;   // ... with at least this many bytes of the snps x n panel per chunk
 };
 Options &options();
 

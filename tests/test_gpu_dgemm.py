@@ -245,7 +245,7 @@ def test_dgemm_host_pipeline_chunks(gpu_lib, snps, indiv, ncol, chunks):
                 assert np.all(Cbig[m:] == 7.25)  # rows beyond m untouched
     finally:
         api.free_compressed(h)
-        gpu_lib.mb200_set_pipeline(4, 4.0e6)
+        gpu_lib.mb200_set_pipeline(4, 1.0e7)
         gpu_lib.mb200_set_dgemm_mode(1, 0)
 
 
@@ -271,7 +271,7 @@ def test_dgemm_host_pipeline_precision_fallback(gpu_lib):
         assert relerr(got, cport.dgemm_compressed("N", plink, snps, indiv, f, B, True)) <= TOL
     finally:
         api.free_compressed(h)
-        gpu_lib.mb200_set_pipeline(4, 4.0e6)
+        gpu_lib.mb200_set_pipeline(4, 1.0e7)
 
 
 @pytest.mark.parametrize("b_dev,c_dev", [(0, 0), (0, 1), (1, 0), (1, 1)])
@@ -305,5 +305,5 @@ def test_dgemm_mixed_host_device_panels(gpu_lib, b_dev, c_dev):
                 assert relerr(got, want) <= TOL, (mode, tr)
     finally:
         api.free_compressed(h)
-        gpu_lib.mb200_set_pipeline(4, 4.0e6)
+        gpu_lib.mb200_set_pipeline(4, 1.0e7)
         gpu_lib.mb200_set_dgemm_mode(1, 0)
