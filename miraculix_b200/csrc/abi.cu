@@ -244,7 +244,7 @@ int mb200_set_pipeline(int chunks, double min_bytes) {
   return 0;
 }
 int mb200_set_crossprod_mode(int mode) {
-  if (mode == 0 || mode == 1) options().crossprod_mode = mode;
+  if (mode >= 0 && mode <= 2) options().crossprod_mode = mode;
   return 0;
 }
 

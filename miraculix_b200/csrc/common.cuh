@@ -189,6 +189,63 @@ __device__ __forceinline__ void mma_i8_ss(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+
+// ---- CTA pair (cluster of 2, tcgen05 cta_group::2) ---------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address of THIS CTA -> shared::cluster address of the same offset in CTA `rank`
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA tile load of one CTA of a pair: data into this CTA's smem, bytes signalled on an mbarrier
+// that may live in the peer CTA (cluster address, e.g. the leader's full barrier).
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const void *tmap, uint32_t bar_cluster,
+                                                 int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(tmap), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t *dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+// MMA-completion -> arrive on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void tc_commit_pair(uint64_t *bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(smem_u32(bar)), "h"(mask)
+      : "memory");
+}
+// M = 256 over the pair (128 rows from each CTA's A tile), B = N/2 rows from each CTA's smem
+__device__ __forceinline__ void mma_i8_ss_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // D[tmem] (+)= A[tmem] * B[smem desc]
 __device__ __forceinline__ void mma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
                                           uint32_t idesc, uint32_t accumulate) {
@@ -278,6 +335,29 @@ __device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t make_idesc_i8(int M, int N, int a_signed, int b_signed) {
   return (2u << 4) | ((uint32_t)a_signed << 7) | ((uint32_t)b_signed << 10) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// ---- exact GRM update shared by the crossproduct epilogues (see crossprod_kernels.cuh) --------
+struct CpAffine {
+  long long n2, total;
+  long n;
+  double scale;
+};
+__device__ __forceinline__ CpAffine cp_affine_setup(long n, int affine, int do_scale,
+                                                    const double *scal) {
+  CpAffine a;
+  a.n = n;
+  a.n2 = (long long)n * (long long)n;
+  a.total = affine ? __double2ll_rn(scal[0]) : 0;
+  a.scale = affine ? (do_scale ? 1.0 / scal[1] : 1.0) / ((double)n * (double)n) : 1.0;
+  return a;
+}
+// ai = n m_i ; bj = n m_j - total
+__device__ __forceinline__ double cp_affine(int count, long long ai, long long bj, const CpAffine &a) {
+  const long long t = (long long)count * a.n2 - ai - bj;
+  return __dmul_rn((double)t, a.scale);
+}
+__device__ __forceinline__ double cp_affine_m(int count, double mi, double mj, const CpAffine &a) {
+  return cp_affine(count, __double2ll_rn(mi) * a.n, __double2ll_rn(mj) * a.n - a.total, a);
 }
 #endif  // __CUDACC__
 

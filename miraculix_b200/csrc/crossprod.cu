@@ -17,11 +17,12 @@ namespace mb200 {
 struct TileCoord;
 int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
                     cudaStream_t stream, int split_kblocks, int grid_max, int *num_tail,
-                    int *real_tiles);
+                    int *real_tiles, int pair);
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream, const CpFinish *finish, int num_tail);
+                        cudaStream_t stream, const CpFinish *finish, int num_tail, int pair);
+int crossprod_tc_units(int sm_count, int pair);
 
 static int upload_lut() {
   uint8_t table[256];
@@ -34,6 +35,9 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
                      const double *d_f, int do_scale, double *d_ans, cudaStream_t stream,
                      CrossprodTiming *timing) {
   if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
+  // the fused GRM update is exact in 64-bit integers: n^2 M with M <= 4 k must stay below 2^62
+  if (mode == 1 && (double)rows * (double)rows * 4.0 * (double)k >= 4.0e18)
+    return fail(-2, __func__, __LINE__, "GRM of %ld x %ld exceeds the exact integer epilogue", rows, k);
   int device = 0;
   MB_CUDA(cudaGetDevice(&device));
   const int sms = device_sm_count(device);
@@ -56,7 +60,10 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   unsigned int *d_s = nullptr;
   TileCoord *d_tiles = nullptr;
   int num_tiles = 0;
-  const int tc = options().crossprod_mode == 1;
+  const int tc = options().crossprod_mode >= 1;
+  // mode 2: 256 x 256 tiles on CTA pairs (tcgen05 cta_group::2); falls back to one CTA per tile
+  // when the device cannot co-schedule pairs
+  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0;
   const int nslabs = (int)ceil_div(nb, slab_kbytes);
   // tensor-core path: the last slab's GEMM epilogue writes the final fp64 matrix itself (counts,
   // or the centred/scaled GRM), so the int32 matrix only exists when K needs several slabs
@@ -71,7 +78,8 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   int real_tiles = 0;
   int num_tail = 0;  // single slab: the last partial round of tiles is cut along K (crossprod_tc.cu)
   const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
-  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles));
+  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream, split_kb,
+                                   crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   // GRM: the row sums m = M 1 come exactly from the input, m = X (X^T 1) (64-bit integers), so
@@ -109,7 +117,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     MB_LAUNCH_CHECK();
     if (tc) {
       MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
-                                   sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail));
+                                   sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, pair));
       executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
     } else {
       const unsigned g = (unsigned)(rows_pad / 64);
@@ -175,6 +183,9 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   if (nparts < 1 || part < 0 || part >= nparts)
     return fail(-2, __func__, __LINE__, "bad partition %d of %d", part, nparts);
   if (mode < 0 || mode > 1) return fail(-2, __func__, __LINE__, "mode %d not supported on panels", mode);
+  // the fused GRM update is exact in 64-bit integers: n^2 M with M <= 4 k must stay below 2^62
+  if (mode == 1 && (double)rows * (double)rows * 4.0 * (double)k >= 4.0e18)
+    return fail(-2, __func__, __LINE__, "GRM of %ld x %ld exceeds the exact integer epilogue", rows, k);
   int device = 0;
   MB_CUDA(cudaGetDevice(&device));
   const int sms = device_sm_count(device);
@@ -209,7 +220,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   int real_tiles = 0;
   int num_tail = 0;
   const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
-  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles));
+  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles, 0));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   if (mode == 1) {
@@ -247,7 +258,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     count_launch();
     MB_LAUNCH_CHECK();
     MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
-                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail));
+                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, 0));
     executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
   }
   MB_CUDA(cudaEventRecord(e2, stream));

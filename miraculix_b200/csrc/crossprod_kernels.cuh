@@ -54,18 +54,16 @@ expand_2bit_kernel(const uint8_t *__restrict__ x, long rows, long nb, long kb0, 
   }
 }
 
-// int32 counts (row-major, ld32, valid where row <= col) -> fp64 full symmetric column-major
-// n x n (reference host loop src/cuda/snp_multiply_cuda.cu:330-340), 32x32 tiles.  With affine != 0
-// the GRM update of crossproduct.jl:95-106 is applied on the way out, in that operation order
-// (M += (-1/n) m_i ; M += (-1/n) m_j ; M += total/n^2 ; M /= c), each step rounded like the BLAS
-// sequence (no FMA contraction): scal[0] = total = sum m, scal[1] = c = 2 sum f (1 - f).
-__device__ __forceinline__ double grm_affine(double v, double mi, double mj, double alpha,
-                                             double shift, double rc, int do_scale) {
-  v = __dadd_rn(v, __dmul_rn(alpha, mi));
-  v = __dadd_rn(v, __dmul_rn(alpha, mj));
-  v = __dadd_rn(v, shift);
-  return do_scale ? __dmul_rn(v, rc) : v;  // rc = 1/c: one ulp from M / c, no fp64 divide per entry
-}
+// int32 counts -> fp64, mirrored into the full symmetric matrix; with `affine` the GRM update of
+// crossproduct.jl:95-106, G = (M - (m_i + m_j)/n + total/n^2) / c, is applied on the way out as
+//   G = (n^2 M - n m_i - (n m_j - total)) * (1 / (c n^2))
+// with the bracket EXACT in 64-bit integers (M, m and total are integers; n^2 * 4k < 2^62 is
+// checked on the host) and one rounding each for the conversion and the scale: at least as
+// accurate as the BLAS sequence of the reference, exactly symmetric, and ONE fp64 instruction per
+// entry instead of twelve (fp64 instructions in the epilogue warps of the tensor-core GEMM stall
+// on the math pipe the MMAs keep busy; they cost a quarter of the GEMM time).
+// scal[0] = total = sum m, scal[1] = c = 2 sum f (1 - f).
+// (CpAffine / cp_affine live in common.cuh: the tensor-core GEMM epilogue uses them too)
 __global__ void __launch_bounds__(256)
 counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
                         double *__restrict__ ans, int affine, const double *__restrict__ m,
@@ -73,9 +71,7 @@ counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
   __shared__ int32_t t[32][33];
   const long bi = blockIdx.x, bj = blockIdx.y;  // output tile: rows i in bi, cols j in bj
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-  const double alpha = -1.0 / (double)n;
-  const double shift = affine ? scal[0] / ((double)n * (double)n) : 0.0;
-  const double c = affine && do_scale ? 1.0 / scal[1] : 1.0;
+  const CpAffine aff = cp_affine_setup(n, affine, do_scale, scal);
   if (bi <= bj) {
     // source M32[i][j], contiguous in j: load (i = ty.., j = tx), transpose through smem
     for (int yy = ty; yy < 32; yy += 8) {
@@ -86,9 +82,7 @@ counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
     for (int yy = ty; yy < 32; yy += 8) {
       const long j = bj * 32 + yy, i = bi * 32 + tx;
       if (i < n && j < n) {
-        double v = (double)t[tx][yy];
-        if (affine) v = grm_affine(v, m[i], m[j], alpha, shift, c, do_scale);
-        ans[i + j * n] = v;
+        ans[i + j * n] = affine ? cp_affine_m(t[tx][yy], m[i], m[j], aff) : (double)t[tx][yy];
       }
     }
   } else {
@@ -96,9 +90,8 @@ counts_to_double_kernel(const int32_t *__restrict__ M32, long ld32, long n,
     for (int yy = ty; yy < 32; yy += 8) {
       const long j = bj * 32 + yy, i = bi * 32 + tx;
       if (i < n && j < n) {
-        double v = (double)M32[j * ld32 + i];
-        if (affine) v = grm_affine(v, m[i], m[j], alpha, shift, c, do_scale);
-        ans[i + j * n] = v;
+        const int cnt = M32[j * ld32 + i];
+        ans[i + j * n] = affine ? cp_affine_m(cnt, m[i], m[j], aff) : (double)cnt;
       }
     }
   }
@@ -129,27 +122,6 @@ reduce_sum_kernel(const double *__restrict__ v, long n, int mode, double *__rest
     acc = red[threadIdx.x];
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (threadIdx.x == 0) *out = mode ? 2.0 * acc : acc;
-  }
-}
-// GRM affine epilogue in the order of crossproduct.jl:95-106:
-//   M += (-1/n) m_i ; M += (-1/n) m_j ; M += total/n^2 ; if do_scale M /= c
-// scal[0] = total, scal[1] = c.  No FMA contraction: each step rounds like the BLAS sequence.
-__global__ void __launch_bounds__(256)
-grm_affine_kernel(double *__restrict__ M, long n, const double *__restrict__ m,
-                  const double *__restrict__ scal, int do_scale) {
-  const long total = n * n;
-  const double alpha = -1.0 / (double)n;
-  const double shift = scal[0] / ((double)n * (double)n);
-  const double c = scal[1];
-  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-       e += (long)gridDim.x * blockDim.x) {
-    const long i = e % n, j = e / n;
-    double v = M[e];
-    v = __dadd_rn(v, __dmul_rn(alpha, m[i]));
-    v = __dadd_rn(v, __dmul_rn(alpha, m[j]));
-    v = __dadd_rn(v, shift);
-    if (do_scale) v = v / c;
-    M[e] = v;
   }
 }
 // LD epilogue (crossproduct.jl:128-152): M -= 4 n_obs f_i f_j ; then / sigma_i / sigma_j with
@@ -369,30 +341,6 @@ inline int input_row_sums(const uint8_t *d_x, long rows, long nb, int is_plink, 
   MB_LAUNCH_CHECK();
   return 0;
 }
-// Compact panel of one partition: local row lr is global row ((lr/128) nparts + part) 128 + lr%128.
-// Columns left of the first computed tile (256 floor(i/256)) are not part of the panel: zero.
-// mode 1 applies the GRM update in the operation order of crossproduct.jl:95-106.
-__global__ void __launch_bounds__(256)
-panel_finish_kernel(const int32_t *__restrict__ C32, long ld32, long local_rows, long n, int part,
-                    int nparts, int mode, const double *__restrict__ m,
-                    const double *__restrict__ scal, int do_scale, double *__restrict__ out) {
-  const long total = local_rows * n;
-  const double alpha = -1.0 / (double)n;
-  const double shift = mode ? scal[0] / ((double)n * (double)n) : 0.0;
-  const double rc = mode && do_scale ? 1.0 / scal[1] : 1.0;
-  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-       e += (long)gridDim.x * blockDim.x) {
-    const long lr = e / n, j = e % n;
-    const long i = ((lr >> 7) * nparts + part) * 128 + (lr & 127);
-    double v = 0.0;
-    if (i < n && j >= ((i >> 8) << 8)) {
-      v = (double)C32[lr * ld32 + j];
-      if (mode) v = grm_affine(v, m[i], m[j], alpha, shift, rc, do_scale);
-    }
-    out[e] = v;
-  }
-}
-
 // mode 0 fallback GEMM: dp4a SIMT, 64x64 output tile per block, upper-triangle blocks only.
 // C32[i][j] (+)= sum_k X8[i][k] X8[j][k]
 __global__ void __launch_bounds__(256)

@@ -21,20 +21,20 @@
 namespace mb200 {
 
 constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 128;  // BK in bytes = int8 elements
-constexpr int TC_STAGES = 4;
 constexpr int TC_A_BYTES = TC_BM * TC_BK;  // 16 KB
 constexpr int TC_B_BYTES = TC_BN * TC_BK;  // 32 KB
-constexpr int TC_STAGE_BYTES = TC_A_BYTES + TC_B_BYTES;
-constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+// One CTA per tile: 4 stages of A + B = 48 KB.  CTA pair (cta_group::2, a 256 x 256 tile over two
+// SMs): every CTA stages its own 128 rows of A and HALF of B (128 of the 256 rows) = 32 KB, 6
+// stages -- per SM a third less L2 -> smem traffic and operand reads per MMA.
+template <bool PAIR> struct TcGeom {
+  static constexpr int STAGES = PAIR ? 6 : 4;
+  static constexpr int STAGE_BYTES = TC_A_BYTES + (PAIR ? TC_B_BYTES / 2 : TC_B_BYTES);
+};
+constexpr int TC_STG = 32 * 33;  // doubles of one epilogue warp's 32 x 32 staging tile (padded)
+constexpr int TC_SMEM = 4 * (TC_A_BYTES + TC_B_BYTES) + 1024 /*align*/ + 256 /*barriers*/ +
+                        4 * TC_STG * 8 /*epilogue staging*/;
+static_assert(TC_SMEM <= 232448, "shared memory budget");
 constexpr int TC_THREADS = 192;
-
-__device__ __forceinline__ double cp_affine(double v, double mr, double mc, double alpha,
-                                            double shift, double rc, int do_scale) {
-  v = __dadd_rn(v, __dmul_rn(alpha, mr));  // same operation order as grm_affine (crossprod_kernels.cuh)
-  v = __dadd_rn(v, __dmul_rn(alpha, mc));
-  v = __dadd_rn(v, shift);
-  return do_scale ? __dmul_rn(v, rc) : v;
-}
 
 struct TileCoord {
   int mi, nj;  // operand tiles: rows mi*128.. of X against rows nj*256.. of X
@@ -46,6 +46,7 @@ struct TileCoord {
   int kb0, kb1, slot;
 };
 
+template <bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b,
@@ -54,12 +55,18 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
+  constexpr int TC_STAGES = TcGeom<PAIR>::STAGES, TC_STAGE_BYTES = TcGeom<PAIR>::STAGE_BYTES;
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES);
   uint64_t *full = bars, *empty = bars + TC_STAGES;
   uint64_t *tfull = bars + 2 * TC_STAGES, *tempty = bars + 2 * TC_STAGES + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * TC_STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // PAIR: the two CTAs of a cluster share one work item (a pair of row tiles mi, mi + 1 against
+  // column tile nj); rank 0 (the leader) issues the MMAs for both, every CTA loads its own operands
+  // and drains its own 128 accumulator rows.
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int unit0 = PAIR ? blockIdx.x >> 1 : blockIdx.x, nunits = PAIR ? gridDim.x >> 1 : gridDim.x;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < TC_STAGES; s++) {
@@ -68,15 +75,19 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int a = 0; a < 2; a++) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 4);  // one arrive per epilogue warp
+      mbar_init(&tempty[a], PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs)
     }
     fence_mbar_init();
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
   }
-  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  if (warp == 0) {
+    if (PAIR) tmem_alloc_pair(tmem_slot, 512);
+    else tmem_alloc(tmem_slot, 512);
+  }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -84,16 +95,25 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // ===== TMA producer (whole warp walks the protocol, one elected lane issues) =====
     int stage = 0;
     uint32_t phase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = unit0; t < num_tiles; t += nunits) {
       const TileCoord tc = tiles[t];
       const int kb1 = tc.kb1 < 0 ? num_kblocks : tc.kb1;
       for (int kb = tc.kb0; kb < kb1; kb++) {
         mbar_wait_warp(&empty[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t *sa = smem + stage * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
-          mbar_expect_tx(&full[stage], TC_STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, &full[stage], kb * TC_BK, tc.mi * TC_BM);
-          tma_load_2d(sb, &tmap_b, &full[stage], kb * TC_BK, tc.nj * TC_BN);
+          if (!PAIR) {
+            mbar_expect_tx(&full[stage], TC_STAGE_BYTES);
+            tma_load_2d(sa, &tmap_a, &full[stage], kb * TC_BK, tc.mi * TC_BM);
+            tma_load_2d(sb, &tmap_b, &full[stage], kb * TC_BK, tc.nj * TC_BN);
+          } else {
+            // all bytes of both CTAs complete on the LEADER's full barrier; tmap_a's 128-row box
+            // serves the A tile and this CTA's half of the B tile
+            if (rank == 0) mbar_expect_tx(&full[stage], 2 * TC_STAGE_BYTES);
+            const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+            tma_load_2d_pair(sa, &tmap_a, lead_full, kb * TC_BK, (tc.mi + rank) * TC_BM);
+            tma_load_2d_pair(sb, &tmap_a, lead_full, kb * TC_BK, tc.nj * TC_BN + rank * (TC_BN / 2));
+          }
         }
         __syncwarp();
         if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
@@ -101,31 +121,46 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else if (warp == 1) {
     // ===== MMA issuer (elect.sync issue: no uniformisation loops around UTCIMMA) =====
-    constexpr uint32_t idesc = make_idesc_i8(TC_BM, TC_BN, 0, 0);
+    constexpr uint32_t idesc = make_idesc_i8(PAIR ? 2 * TC_BM : TC_BM, TC_BN, 0, 0);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    bool ready = false;
+    for (int t = unit0; t < num_tiles && rank == 0; t += nunits) {
       mbar_wait_warp(&tempty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * TC_BN;
       const int kb0 = tiles[t].kb0, kb1 = tiles[t].kb1 < 0 ? num_kblocks : tiles[t].kb1;
       for (int kb = kb0; kb < kb1; kb++) {
-        mbar_wait_warp(&full[stage], phase);
+        if (!ready) mbar_wait_warp(&full[stage], phase);
         tc_fence_after();
+        // a try_wait costs ~90 cycles even on a completed phase: probe the NEXT stage now
+        // (non-blocking) and consume the answer after this stage's MMAs are issued
+        const int stage_n = stage + 1 == TC_STAGES ? 0 : stage + 1;
+        const uint32_t phase_n = stage + 1 == TC_STAGES ? phase ^ 1 : phase;
+        const bool poll = mbar_test_wait(&full[stage_n], phase_n);
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * TC_STAGE_BYTES);
           const uint64_t adesc = make_desc_k_sw128(sa);
           const uint64_t bdesc = make_desc_k_sw128(sa + TC_A_BYTES);
 #pragma unroll
-          for (int k4 = 0; k4 < TC_BK / 32; k4++)  // +32 bytes along K = +2 in the >>4 address field
-            mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb > kb0 || k4) ? 1u : 0u);
-          tc_commit(&empty[stage]);
-          if (kb == kb1 - 1) tc_commit(&tfull[acc]);
+          for (int k4 = 0; k4 < TC_BK / 32; k4++) {  // +32 bytes along K = +2 in the >>4 address field
+            if (PAIR) mma_i8_ss_pair(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb > kb0 || k4) ? 1u : 0u);
+            else mma_i8_ss(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (kb > kb0 || k4) ? 1u : 0u);
+          }
+          if (PAIR) {  // the stage is free, and the accumulator ready, in BOTH CTAs
+            tc_commit_pair(&empty[stage], 3);
+            if (kb == kb1 - 1) tc_commit_pair(&tfull[acc], 3);
+          } else {
+            tc_commit(&empty[stage]);
+            if (kb == kb1 - 1) tc_commit(&tfull[acc]);
+          }
         }
         __syncwarp();
-        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        ready = __all_sync(0xffffffffu, poll);
+        stage = stage_n;
+        phase = phase_n;
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -134,11 +169,15 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int quad = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    const double alpha = fin.kind ? -1.0 / (double)fin.n : 0.0;
-    const double shift = fin.affine ? fin.scal[0] / ((double)fin.n * (double)fin.n) : 0.0;
-    const double rc = fin.affine && fin.do_scale ? 1.0 / fin.scal[1] : 1.0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const TileCoord tc = tiles[t];
+    const CpAffine aff = cp_affine_setup(fin.n, fin.affine, fin.do_scale, fin.scal);
+    double *stg = reinterpret_cast<double *>(smem + TC_STAGES * TC_STAGE_BYTES + 256) + (warp - 2) * TC_STG;
+    for (int t = unit0; t < num_tiles; t += nunits) {
+      TileCoord tc = tiles[t];
+      if (PAIR) {  // this CTA's half of the pair
+        tc.mi += rank;
+        tc.mo += rank;
+        if (tc.slot >= 0) tc.slot = 2 * tc.slot + rank;
+      }
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const long row = (long)tc.mo * TC_BM + quad * 32 + lane;
@@ -148,7 +187,7 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const long gi = fin.kind == 2 ? ((long)tc.mo * fin.nparts + fin.part) * TC_BM + quad * 32 + lane
                                     : row;
       const bool iok = fin.kind && gi < fin.n;
-      const double mi = (fin.affine && iok) ? fin.m[gi] : 0.0;
+      const long long ai = (fin.affine && iok) ? __double2ll_rn(fin.m[gi]) * aff.n : 0;
 #pragma unroll 1
       for (int c = 0; c < TC_BN / 32; c++) {
         uint32_t r[32];
@@ -185,54 +224,55 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const long j0 = (long)tc.nj * TC_BN + c * 32;
         // row sums of this chunk's 32 columns: one per lane (read-only path), broadcast by shuffle
         // -- a plain m[j] load inside the store loop is serialised behind the stores (aliasing)
-        const double mlane = (fin.affine && j0 + lane < fin.n) ? __ldg(fin.m + j0 + lane) : 0.0;
-        double mjv[32];
+        const long long blane =
+            (fin.affine && j0 + lane < fin.n) ? __double2ll_rn(__ldg(fin.m + j0 + lane)) * aff.n - aff.total : 0;
+        long long bjv[32];
 #pragma unroll
-        for (int q = 0; q < 32; q++) mjv[q] = __shfl_sync(0xffffffffu, mlane, q);
-        if (!iok) {
-          // padding row: nothing to write (stay converged for the next collective tcgen05.ld)
-        } else if (fin.kind == 1) {
-          double *col = fin.out + gi + j0 * fin.n;      // (i, j0 + q): lanes = consecutive i
-          double *mir = fin.out + j0 + gi * fin.n;      // (j0 + q, i): this thread's own column
+        for (int q = 0; q < 32; q++) bjv[q] = __shfl_sync(0xffffffffu, blane, q);
+        // Stores whose consecutive addresses belong to ONE thread (the mirrored element of the full
+        // matrix, the row-major panel of a partition) would cost 32 L1 wavefronts per instruction
+        // and starve the tensor core's operand reads, which share the L1 data pipe: the 32 x 32
+        // block goes through a per-warp staging tile and leaves with lanes = consecutive addresses.
+        const long rowbase = gi - lane;  // global row of lane 0's thread
+        double *col = fin.out + gi + j0 * fin.n;        // kind 1: (i, j0 + q), lanes = consecutive i
 #pragma unroll
-          for (int q = 0; q < 32; q++) {
-            const long j = j0 + q;
-            if (j < fin.n && gi <= j) {
-              const double v = (double)(int)r[q];
-              if (fin.affine) {
-                const double mj = mjv[q];
-                col[(long)q * fin.n] = cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale);
-                mir[q] = cp_affine(v, mj, mi, alpha, shift, rc, fin.do_scale);
-              } else {
-                col[(long)q * fin.n] = v;
-                mir[q] = v;
-              }
-            }
+        for (int q = 0; q < 32; q++) {
+          const double v = fin.affine ? cp_affine((int)r[q], ai, bjv[q], aff) : (double)(int)r[q];
+          stg[lane * 33 + q] = v;
+          if (fin.kind == 1 && iok && j0 + q < fin.n && gi <= j0 + q) col[(long)q * fin.n] = v;
+        }
+        __syncwarp();
+        const long j = j0 + lane;                       // this lane's column of the 32 x 32 block
+        if (fin.kind == 1) {                            // mirrored element (j, i): exactly symmetric
+#pragma unroll 8
+          for (int i = 0; i < 32; i++) {
+            const long gr = rowbase + i;
+            if (j < fin.n && gr < fin.n && gr <= j) fin.out[j + gr * fin.n] = stg[i * 33 + lane];
           }
-        } else {
-          double *prow = fin.out + row * fin.n + j0;
-#pragma unroll
-          for (int q = 0; q < 32; q++) {
-            const long j = j0 + q;
-            if (j < fin.n) {
-              const double v = (double)(int)r[q];
-              prow[q] = fin.affine ? cp_affine(v, mi, mjv[q], alpha, shift, rc, fin.do_scale) : v;
-            }
-          }
+        } else {                                        // row-major panel of a partition
+          double *pblock = fin.out + (row - lane) * fin.n + j;
+#pragma unroll 8
+          for (int i = 0; i < 32; i++)
+            if (j < fin.n && rowbase + i < fin.n) pblock[(long)i * fin.n] = stg[i * 33 + lane];
         }
         __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if (PAIR && rank) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));  // the issuer waits on rank 0's
+        else mbar_arrive(&tempty[acc]);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the leader's MMAs read the peer's smem and write its TMEM
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc_pair(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -282,9 +322,7 @@ __global__ void __launch_bounds__(256)
 tail_finish_kernel(const TileCoord *__restrict__ tail_tiles, const int *__restrict__ scratch,
                    const CpFinish fin) {
   const TileCoord tc = tail_tiles[blockIdx.x];
-  const double alpha = -1.0 / (double)fin.n;
-  const double shift = fin.affine ? fin.scal[0] / ((double)fin.n * (double)fin.n) : 0.0;
-  const double rc = fin.affine && fin.do_scale ? 1.0 / fin.scal[1] : 1.0;
+  const CpAffine aff = cp_affine_setup(fin.n, fin.affine, fin.do_scale, fin.scal);
   const int *src = scratch + (long)blockIdx.x * TC_BM * TC_BN;
   for (int e = threadIdx.x; e < TC_BM * TC_BN; e += 256) {
     // kind 1 stores column-major (consecutive threads = consecutive rows), kind 2 row-major
@@ -293,14 +331,14 @@ tail_finish_kernel(const TileCoord *__restrict__ tail_tiles, const int *__restri
     const long gi = fin.kind == 2 ? ((long)tc.mo * fin.nparts + fin.part) * TC_BM + r : lrow;
     const long j = (long)tc.nj * TC_BN + c;
     if (gi >= fin.n || j >= fin.n) continue;
-    const double v = (double)src[r * TC_BN + c];
-    const double mi = fin.affine ? fin.m[gi] : 0.0, mj = fin.affine ? fin.m[j] : 0.0;
+    const int cnt = src[r * TC_BN + c];
+    const double v = fin.affine ? cp_affine_m(cnt, fin.m[gi], fin.m[j], aff) : (double)cnt;
     if (fin.kind == 1) {
       if (gi > j) continue;
-      fin.out[gi + j * fin.n] = fin.affine ? cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale) : v;
-      fin.out[j + gi * fin.n] = fin.affine ? cp_affine(v, mj, mi, alpha, shift, rc, fin.do_scale) : v;
+      fin.out[gi + j * fin.n] = v;
+      fin.out[j + gi * fin.n] = v;
     } else {
-      fin.out[lrow * fin.n + j] = fin.affine ? cp_affine(v, mi, mj, alpha, shift, rc, fin.do_scale) : v;
+      fin.out[lrow * fin.n + j] = v;
     }
   }
 }
@@ -310,14 +348,25 @@ tail_finish_kernel(const TileCoord *__restrict__ tail_tiles, const int *__restri
 // at (*d_tiles)[*num_tiles ...].
 int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *num_tiles,
                     cudaStream_t stream, int split_kblocks, int grid_max, int *num_tail,
-                    int *real_tiles) {
+                    int *real_tiles, int pair) {
   const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
   std::vector<TileCoord> v;
-  for (int sn = 0; sn < Nt; sn += 8)
-    for (int sm = 0; sm < Mt; sm += 16 * nparts)
-      for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
-        for (int mi = sm + part; mi < sm + 16 * nparts && mi < Mt; mi += nparts)
-          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts, 0, -1, -1});
+  if (pair) {
+    // work items = pairs of row tiles (2 Mi, 2 Mi + 1) against column tile nj >= Mi: both halves of
+    // such a pair are upper-triangle tiles (the operand is padded to a multiple of 256 rows)
+    if (nparts != 1) return fail(-2, __func__, __LINE__, "CTA-pair tiles are not partitioned");
+    for (int sn = 0; sn < Nt; sn += 8)
+      for (int sm = 0; sm < Mt; sm += 16)
+        for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
+          for (int mi = sm; mi < sm + 16 && mi < Mt; mi += 2)
+            if (nj >= mi / 2) v.push_back({mi, nj, mi, 0, -1, -1});
+  } else {
+    for (int sn = 0; sn < Nt; sn += 8)
+      for (int sm = 0; sm < Mt; sm += 16 * nparts)
+        for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
+          for (int mi = sm + part; mi < sm + 16 * nparts && mi < Mt; mi += nparts)
+            if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts, 0, -1, -1});
+  }
   int ntail = 0;
   const int T = (int)v.size();
   if (split_kblocks > 0 && grid_max > 0 && T > grid_max) {
@@ -334,14 +383,17 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
           c.slot = t;
           v.push_back(c);
         }
-      ntail = rem;
+      ntail = pair ? 2 * rem : rem;                      // scratch tiles of 128 x 256
       *num_tiles = (int)v.size();
-      v.insert(v.end(), tail.begin(), tail.end());
+      for (const TileCoord &c : tail) {                  // finish list: one entry per scratch tile
+        v.push_back(c);
+        if (pair) v.push_back({c.mi + 1, c.nj, c.mo + 1, 0, -1, -1});
+      }
     }
   }
   if (!ntail) *num_tiles = T;
   if (num_tail) *num_tail = ntail;
-  if (real_tiles) *real_tiles = T;
+  if (real_tiles) *real_tiles = pair ? 2 * T : T;
   if (v.empty()) v.push_back({0, 0, 0, 0, -1, -1});  // keep the allocation non-empty; the launch is skipped
   MB_CUDA(cudaMallocAsync(d_tiles, sizeof(TileCoord) * v.size(), stream));
   MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice,
@@ -350,17 +402,44 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
   return 0;
 }
 
+// Work items one launch keeps in flight: CTAs (one per SM) or CTA pairs (clusters of 2).
+int crossprod_tc_units(int sm_count, int pair) {
+  if (!pair) return sm_count;
+  static int clusters = -1;
+  if (clusters < 0) {
+    cudaFuncSetAttribute(crossprod_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * sm_count);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = TC_SMEM;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = 2;
+    at.val.clusterDim.y = 1;
+    at.val.clusterDim.z = 1;
+    cfg.attrs = &at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, crossprod_tc_kernel<true>, &cfg) != cudaSuccess || n < 1) {
+      cudaGetLastError();
+      n = 0;
+    }
+    clusters = n < sm_count / 2 ? n : sm_count / 2;
+  }
+  return clusters;
+}
+
 int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
-                        cudaStream_t stream, const CpFinish *finish, int num_tail) {
-  MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               TC_SMEM));
+                        cudaStream_t stream, const CpFinish *finish, int num_tail, int pair) {
   CUtensorMap ta, tb;
   MB_CHECK(make_tmap_u8_2d(&ta, X8, kcols, rows_pad, pitch, TC_BK, TC_BM, 1));
   MB_CHECK(make_tmap_u8_2d(&tb, X8, kcols, rows_pad, pitch, TC_BK, TC_BN, 1));
   if (num_tiles <= 0) return 0;
-  const int grid = num_tiles < sm_count ? num_tiles : sm_count;
+  const int units = crossprod_tc_units(sm_count, pair);
+  if (units < 1) return fail(-12, __func__, __LINE__, "no co-resident CTA pairs on this device");
+  const int grid = (num_tiles < units ? num_tiles : units) * (pair ? 2 : 1);
   CpFinish fin = finish ? *finish : CpFinish();
   int *scratch = nullptr;
   if (num_tail > 0) {
@@ -370,9 +449,28 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
     MB_CUDA(cudaMemsetAsync(scratch, 0, bytes, stream));
     fin.tail = scratch;
   }
-  crossprod_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
-                                                             (int)(kcols / TC_BK), C32, ld32,
-                                                             accumulate, fin);
+  if (pair) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = TC_SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = 2;
+    at.val.clusterDim.y = 1;
+    at.val.clusterDim.z = 1;
+    cfg.attrs = &at;
+    cfg.numAttrs = 1;
+    MB_CUDA(cudaLaunchKernelEx(&cfg, crossprod_tc_kernel<true>, ta, tb, d_tiles, num_tiles,
+                               (int)(kcols / TC_BK), C32, ld32, accumulate, fin));
+  } else {
+    MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel<false>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+    crossprod_tc_kernel<false><<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
+                                                                      (int)(kcols / TC_BK), C32, ld32,
+                                                                      accumulate, fin);
+  }
   count_launch();
   MB_LAUNCH_CHECK();
   if (num_tail > 0) {

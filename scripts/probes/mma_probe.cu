@@ -7,7 +7,7 @@
 #include "common.cuh"
 using namespace mb200;
 
-template <int TS, int NACC, int ELECT>
+template <int TS, int NACC, int ELECT, int MMAS = 16>
 __global__ void __launch_bounds__(128, 1) probe(int N, int iters, long long *out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int iters, long long *out
     for (int it = 0; it < iters; it++) {
       if (!ELECT || elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
+        for (int k = 0; k < MMAS; k++) {
           const uint32_t dd = tm + (k % NACC) * N;
           if (TS) mma_i8_ts(dd, tm + 384 + 8 * (k & 3), bdesc + 2 * (k & 3), idesc, 1);
           else mma_i8_ss(dd, adesc + 2 * (k & 3), bdesc + 2 * (k & 3), idesc, 1);
@@ -49,10 +49,10 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int iters, long long *out
   if (threadIdx.x < 32) { tc_fence_after(); tmem_dealloc(tm, 512); }
 }
 
-template <int TS, int NACC, int ELECT>
+template <int TS, int NACC, int ELECT, int MMAS = 16>
 void run(long long *d) {
   long long h;
-  auto kern = probe<TS, NACC, ELECT>;
+  auto kern = probe<TS, NACC, ELECT, MMAS>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
   const int Ns[] = {16, 32, 64, 80, 96, 128, 256};
   for (int N : Ns) {
@@ -62,14 +62,15 @@ void run(long long *d) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); exit(1); }
     cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
-    printf("%s nacc=%d %s N=%3d  cycles/mma=%6.1f (floor %d)\n", TS ? "TS" : "SS", NACC,
-           ELECT ? "elect " : "lane0 ", N, (double)h / (iters * 16), N / 2);
+    printf("%s nacc=%d %s mmas/commit=%d N=%3d  cycles/mma=%6.1f (floor %d)\n", TS ? "TS" : "SS", NACC,
+           ELECT ? "elect " : "lane0 ", MMAS, N, (double)h / (iters * MMAS), N / 2);
   }
 }
 
 int main() {
   long long *d;
   cudaMalloc(&d, 8);
+  run<0, 1, 1, 64>(d); run<0, 2, 1, 64>(d);  // SS, long dependent chains into 1 or 2 accumulators
   run<0, 1, 0>(d); run<0, 1, 1>(d); run<0, 4, 1>(d);
   run<1, 1, 0>(d); run<1, 1, 1>(d); run<1, 2, 1>(d); run<1, 4, 1>(d);
   return 0;

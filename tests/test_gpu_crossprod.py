@@ -27,7 +27,7 @@ def exact_counts(vals):
     return v @ v.T
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 2])
 @pytest.mark.parametrize("snps,indiv", [(953, 752), (64, 5), (129, 257), (2051, 1343),
                                         (10251, 5343)])
 def test_counts_bit_exact(gpu_lib, snps, indiv, mode):
@@ -40,14 +40,14 @@ def test_counts_bit_exact(gpu_lib, snps, indiv, mode):
     try:
         M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False)
     finally:
-        gpu_lib.mb200_set_crossprod_mode(1)
+        gpu_lib.mb200_set_crossprod_mode(2)
     assert np.array_equal(M, M.T)  # crossproduct.jl:61
     if snps * indiv <= 4e6:
         assert np.array_equal(M, cport.crossprod(x, snps, indiv))
     assert np.array_equal(M, exact_counts(Z))
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 2])
 def test_plink_format_table_and_missing_quirk(gpu_lib, mode):
     """is_plink_format=True: bytes go through the reference table; a byte with a missing code
     counts as four 3s, exactly like the reference."""
@@ -60,7 +60,7 @@ def test_plink_format_table_and_missing_quirk(gpu_lib, mode):
     try:
         M = api.snp_crossprod(x, snps, indiv, is_snpmajor=False, is_plink_format=True)
     finally:
-        gpu_lib.mb200_set_crossprod_mode(1)
+        gpu_lib.mb200_set_crossprod_mode(2)
     assert np.array_equal(M, cport.crossprod(x, snps, indiv, True))
     lut = np.load(os.path.join(GOLDEN, "plink2twobit_lut.npy"))
     vals = simulate.unpack_2bit(lut[x], x.shape[1] * 4)
@@ -92,6 +92,30 @@ def test_grm_matches_oracle(gpu_lib, snps, indiv):
     Zc = Z - 2.0 * f[None, :]
     G = api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
     assert relerr(G, Zc @ Zc.T / (2.0 * np.sum(f * (1.0 - f)))) <= 1e-9
+
+
+@pytest.mark.parametrize("snps,indiv", [(2051, 1343), (9300, 3000)])
+def test_grm_identical_over_gemm_paths(gpu_lib, snps, indiv):
+    """SIMT (0), one CTA per tile (1) and CTA pairs (2, tcgen05 cta_group::2) produce the same counts
+    and -- the centring is exact integer arithmetic with one final scale -- bit-identical, exactly
+    symmetric GRMs."""
+    from miraculix_b200 import api
+    _, Z, f = simulate.simulate(snps, indiv, seed=snps + 1)
+    x = simulate.pack_2bit(Z)
+    res = []
+    try:
+        for mode in (0, 1, 2):
+            gpu_lib.mb200_set_crossprod_mode(mode)
+            res.append((api.snp_crossprod(x, snps, indiv, is_snpmajor=False),
+                        api.grm(x, snps, indiv, do_scale=True, allele_freq=f)))
+    finally:
+        gpu_lib.mb200_set_crossprod_mode(2)
+    for M, G in res[1:]:
+        assert np.array_equal(M, res[0][0])
+        assert np.array_equal(G, res[0][1])
+    assert np.array_equal(res[2][1], res[2][1].T)
+    want = cport.grm_epilogue(exact_counts(Z), f, True)
+    assert relerr(res[2][1], want) <= TOL
 
 
 def test_ld_matches_oracle(gpu_lib):
