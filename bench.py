@@ -502,6 +502,62 @@ def run_grm_partition(args, lib, api, dev, rank, world, snps, indiv, label, reps
                          "note": "achieved = EXECUTED ops of all ranks / (max expand+GEMM time x N)"}}
 
 
+def library_int8_peak(dev, indiv, snps):
+    """cuBLASLt int8 GEMM (torch._int_mm) on this box, as the MEASURED int8 denominator SURVEY 8(d)
+    asks for beside the nominal 4.5 POPS: a square 8192^3 product and the GRM's own shape as a plain
+    full-matrix int8 GEMM (no expansion from 2 bits, no symmetry, no fp64 epilogue).  Library calls,
+    reported only; never on the product path."""
+    import torch
+    out = {}
+    try:
+        def timed(m, k, n, reps=10):
+            a = torch.randint(-2, 3, (m, k), dtype=torch.int8, device=dev)
+            b = torch.randint(-2, 3, (n, k), dtype=torch.int8, device=dev).t()
+            for _ in range(3):
+                torch._int_mm(a, b)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+            torch.cuda.synchronize()
+            ev[0].record()
+            for i in range(reps):
+                torch._int_mm(a, b)
+                ev[i + 1].record()
+            torch.cuda.synchronize()
+            ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(reps)]
+            return 2.0 * m * k * n / 1e12, min(ms), statistics.mean(ms)
+        tera, best, mean = timed(8192, 8192, 8192)
+        out["square_8192"] = {"best_tops": tera / (best * 1e-3), "mean_tops": tera / (mean * 1e-3)}
+        m = (indiv + 7) // 8 * 8
+        k = (snps + 7) // 8 * 8
+        tera, best, mean = timed(m, k, m)
+        out["grm_shape_full_matrix"] = {"m": m, "k": k, "best_ms": best, "mean_ms": mean,
+                                        "best_tops": tera / (best * 1e-3), "mean_tops": tera / (mean * 1e-3)}
+        out["how"] = "torch._int_mm (cuBLASLt int8 -> int32), 10 back-to-back calls after 3 warm-ups, CUDA events"
+    except Exception as e:  # reported figure only
+        out["error"] = repr(e)
+    return out
+
+
+def _device_bytes(ptr, nbytes, dev):
+    """uint8 torch view of a library-owned device buffer (no copy)."""
+    import torch
+
+    class _Holder:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False),
+                                    "version": 3, "strides": None}
+    return torch.as_tensor(_Holder(), device=dev)
+
+
+def _grm_traffic(snps, indiv):
+    """DRAM bytes per crossprod_tc_kernel launch from the committed ncu capture (default shape only)."""
+    tfile = os.path.join(ROOT, "profiles", "traffic.json")
+    if (snps, indiv) != (50_000, 10_000) or not os.path.exists(tfile):
+        return None
+    try:
+        return json.load(open(tfile)).get("grm_bytes_per_launch")
+    except Exception:
+        return None
+
+
 def run_grm(args, lib, api, dev):
     """Second half of the metric: centred GRM of configs[1] (50k SNPs x 10k individuals)."""
     import torch
@@ -530,19 +586,49 @@ def run_grm(args, lib, api, dev):
             epi.append(t["epilogue_ms"])
             ops = t["executed_ops"]
     torch.cuda.synchronize()
+    # end to end through the reference-facing host call (mb200_grm = snp_multiply_gpu + the fused
+    # crossproduct.jl:83-110 epilogue): packed matrix and fp64 result in pinned HOST memory, both
+    # PCIe copies and the device allocations inside the timed region (wall clock, the call blocks).
+    e2e = None
+    try:
+        nbytes = indiv * lay.pitch_indiv_major
+        hx = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        hx.copy_(_device_bytes(lay.d_indiv_major, nbytes, dev))
+        hf = f.cpu().pin_memory()
+        hans = torch.empty(indiv * indiv, dtype=torch.float64, pin_memory=True)
+        ts = []
+        for it in range(4):
+            t0 = time.perf_counter()
+            api._check(lib.mb200_grm(C.c_void_p(hx.data_ptr()), kcols, indiv, C.c_void_p(hans.data_ptr()),
+                                     False, C.c_void_p(hf.data_ptr()), True), "mb200_grm")
+            if it >= 1:
+                ts.append(time.perf_counter() - t0)
+        same = bool(torch.equal(hans, ans.cpu()))
+        e2e = {"value": 2.0 * indiv * indiv * snps / statistics.mean(ts) / 1e12, "unit": "TOPS",
+               "ms": statistics.mean(ts) * 1e3, "best_ms": min(ts) * 1e3,
+               "h2d_bytes_per_step": nbytes + 8 * kcols, "d2h_bytes_per_step": 8 * indiv * indiv,
+               "api": "mb200_grm() host call, pinned host buffers, 3 calls after 1 warm-up",
+               "matches_device_result": same}
+        del hx, hans
+    except Exception as e:  # the leg is reported, never fatal for the headline
+        e2e = {"error": repr(e)}
     lib.free_compressed(C.byref(h))
     alg_ops = 2.0 * indiv * indiv * snps
     gm = statistics.mean(gemm)
     tot = gm + statistics.mean(epi)
     int8_peak = 4500.0  # nominal dense int8 TOPS per B200 (no int8 entry in MEASURED_PEAKS.json)
-    return {"workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals (BASELINE configs[1])",
+    lib_int8 = library_int8_peak(dev, indiv, snps)
+    return {"library_int8": lib_int8, "e2e": e2e,
+            "workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals (BASELINE configs[1])",
             "metric": "GRM crossproduct int8 TOPS", "value": alg_ops / (tot * 1e-3) / 1e12,
             "unit": "TOPS (2*indiv^2*snps / t, full-matrix count)", "ms": tot,
             "expand_gemm_ms": gm, "epilogue_ms": statistics.mean(epi),
             "roofline": {"bound": "tensor", "achieved": ops / (gm * 1e-3) / 1e12, "peak": int8_peak,
                          "unit": "TOP/s", "frac": ops / (gm * 1e-3) / 1e12 / int8_peak,
-                         "traffic": None, "peak_source": "nominal int8 dense",
-                         "note": "achieved = EXECUTED ops (upper-triangle tiles only) / expand+GEMM time"}}
+                         "traffic": _grm_traffic(snps, indiv), "peak_source": "nominal int8 dense",
+                         "peak_measured_library": (lib_int8.get("square_8192") or {}).get("best_tops"),
+                         "note": "achieved = EXECUTED ops (upper-triangle tiles only) / expand+GEMM time; "
+                                 "peak_measured_library = cuBLASLt int8 8192^3 on this box"}}
 
 
 def run_cpu_baseline(args):

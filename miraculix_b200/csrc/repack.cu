@@ -317,12 +317,26 @@ rowsum_max_kernel(const uint8_t *__restrict__ A, long pitch, long rows, unsigned
   }
   if (lane == 0 && best) atomicMax(out, best);
 }
+// The SNP-major row sums ARE the allele counts the repack kernels accumulate (after the missing ->
+// 0 recode and the edge mask), so that orientation's maximum is a reduction over 8 bytes per SNP
+// instead of a second read of the whole packed matrix.
+__global__ void __launch_bounds__(256)
+counts_max_kernel(const unsigned long long *__restrict__ counts, long snps, unsigned int *__restrict__ out) {
+  unsigned long long best = 0;
+  for (long j = (long)blockIdx.x * blockDim.x + threadIdx.x; j < snps; j += (long)gridDim.x * blockDim.x) {
+    const unsigned long long c = __ldg(counts + j);
+    best = c > best ? c : best;
+  }
+  unsigned int b32 = (unsigned int)best;                  // <= 2 * indiv < 2^32 (indiv is an int)
+  b32 = __reduce_max_sync(0xffffffffu, b32);
+  if ((threadIdx.x & 31) == 0 && b32) atomicMax(out, b32);
+}
 int rowsum_maxima(Handle *h) {
   unsigned int *d = reinterpret_cast<unsigned int *>(h->d_w);  // scratch, free at creation time
   unsigned int host[2] = {0, 0};
   MB_CUDA(cudaMemsetAsync(d, 0, 2 * sizeof(unsigned int), h->stream));
   rowsum_max_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_indiv_major, h->pitch_i, h->indiv, d);
-  rowsum_max_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_snp_major, h->pitch_s, h->snps, d + 1);
+  counts_max_kernel<<<h->sm_count * 4, 256, 0, h->stream>>>(h->d_counts, h->snps, d + 1);
   count_launch(2);
   MB_LAUNCH_CHECK();
   MB_CUDA(cudaMemcpyAsync(host, d, sizeof(host), cudaMemcpyDeviceToHost, h->stream));

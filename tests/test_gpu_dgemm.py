@@ -182,6 +182,66 @@ def test_dgemm_linearity_and_transpose_identity_large(gpu_lib):
         api.free_compressed(h)
 
 
+def test_dgemm_full_size_properties_and_spot_parity(gpu_lib):
+    """BASELINE configs[2] at FULL size (1M SNPs x 100k individuals, ncol = 10, device-simulated bed):
+    (1) <U, A V> == <A^T U, V> over all ten columns, (2) rows of the 'N' result and of the 'T' result
+    for a handful of individuals / SNPs against a plain numpy long-double product on genotypes
+    decoded straight from the simulated bed (independent of the repack and of both kernels),
+    (3) the stored allele frequencies against the same decode.  Skips on a GPU without ~90 GB free."""
+    import torch
+    from miraculix_b200 import api
+    snps, indiv, n = 1_000_000, 100_000, 10
+    bs = (indiv + 3) // 4
+    free_b, _ = torch.cuda.mem_get_info()
+    if free_b < 90e9:
+        pytest.skip("needs ~90 GB of free device memory")
+    d_plink = torch.empty(snps * bs, dtype=torch.uint8, device="cuda")
+    assert gpu_lib.mb200_simulate_plink_device(d_plink.data_ptr(), snps, indiv, 20261104) == 0
+    h = C.c_void_p(None)
+    assert gpu_lib.mb200_plink2compressed_device(d_plink.data_ptr(), snps, indiv, None, n,
+                                                 C.byref(h)) == 0
+    try:
+        g = torch.Generator(device="cuda").manual_seed(7)
+        V = torch.randn(n, snps, dtype=torch.float64, device="cuda", generator=g)   # col-major snps x n
+        U = torch.randn(n, indiv, dtype=torch.float64, device="cuda", generator=g)  # col-major indiv x n
+        AV = torch.empty(n, indiv, dtype=torch.float64, device="cuda")
+        AtU = torch.empty(n, snps, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        assert gpu_lib.mb200_dgemm_compressed_device(0, h, n, V.data_ptr(), snps, AV.data_ptr(), indiv) == 0
+        assert gpu_lib.mb200_dgemm_compressed_device(1, h, n, U.data_ptr(), indiv, AtU.data_ptr(), snps) == 0
+        assert gpu_lib.mb200_sync(h) == 0
+        lhs = (U * AV).sum(dim=1).cpu().numpy()
+        rhs = (AtU * V).sum(dim=1).cpu().numpy()
+        scale = (U.norm(dim=1) * AV.norm(dim=1)).cpu().numpy()
+        assert (np.abs(lhs - rhs) <= 1e-10 * scale).all()
+
+        f = api.get_compressed_freq(h, snps)
+        bed = d_plink.view(snps, bs)
+        dec = np.array([0.0, 0.0, 1.0, 2.0])                      # PLINK code -> value (MXinfo.h:143)
+        # 'N' rows: individuals i -> z_i[s] for all SNPs, from byte column i // 4 of the bed
+        rows_n = [0, 1, 77_777, 99_999]
+        Vh = V.cpu().numpy().T.astype(np.longdouble)                # snps x n
+        corr = 2.0 * (f.astype(np.longdouble) @ Vh)                 # centring: -2 f^T V
+        for i in rows_n:
+            col = bed[:, i // 4].cpu().numpy()
+            z = dec[(col >> (2 * (i % 4))) & 3].astype(np.longdouble)
+            want = (z @ Vh - corr).astype(np.float64)
+            got = AV[:, i].cpu().numpy()
+            assert np.abs(got - want).max() <= TOL * float(AV.abs().max())
+        # 'T' rows: SNPs s -> z[:, s] for all individuals, from bed row s
+        Uh = U.cpu().numpy().T.astype(np.longdouble)                # indiv x n
+        colsum = Uh.sum(axis=0)
+        for sidx in [0, 513, 500_000, 999_999]:
+            row = bed[sidx].cpu().numpy()
+            z = dec[(row[:, None] >> np.array([0, 2, 4, 6])) & 3].reshape(-1)[:indiv].astype(np.longdouble)
+            want = (z @ Uh - 2.0 * np.longdouble(f[sidx]) * colsum).astype(np.float64)
+            got = AtU[:, sidx].cpu().numpy()
+            assert np.abs(got - want).max() <= TOL * float(AtU.abs().max())
+            assert abs(f[sidx] - float(z.sum()) / (2.0 * indiv)) <= 1e-15
+    finally:
+        api.free_compressed(h)
+
+
 def test_device_pointer_entry_and_simulator(gpu_lib):
     """mb200_plink2compressed_device + mb200_dgemm_compressed_device on torch device buffers; the
     on-device simulator output is a valid bed (no missing codes, zero pad bits) and is
