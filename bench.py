@@ -375,6 +375,12 @@ def run_ours(args):
         except Exception as exc:  # the CPU checker must never take the GPU line down
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                                     "sample": f"failed: {exc}"}
+        if rank == 0 and world == 1 and isinstance(line.get("grm"), dict):
+            try:
+                line["grm"]["cpu_baseline"] = run_grm_cpu_baseline()
+            except Exception as exc:
+                line["grm"]["cpu_baseline"] = {"value": None, "unit": "TOPS", "cores": 0,
+                                               "kind": "reference", "sample": f"failed: {exc}"}
     print(json.dumps(line))
 
 
@@ -642,6 +648,36 @@ def run_cpu_baseline(args):
             "sample": f"{snps} SNPs x {indiv} individuals sub-block, ncol={args.ncol}, 'N'+'T' per step, "
                       f"3 steps after 1 warm-up, reference CPU 5codes variant 256, {cores} threads; "
                       f"{sec:.2f} s/step"}
+
+
+def run_grm_cpu_baseline(snps=16_000, indiv=2_000):
+    """GRM counts on the reference CPU 5codes library: dgemm_compressed('N', not
+    centred) applied to B = Z^T as doubles gives Z Z^T exactly; bounded sample, all host threads."""
+    import numpy as np
+    from oracle import ref, simulate
+    cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    plink, _, f = simulate.simulate(snps, indiv, seed=2)
+    Z = simulate.plink_decode(simulate.unpack_2bit(plink, ((indiv + 3) // 4) * 4)[:, :indiv])
+    B = np.asfortranarray(Z.astype(np.float64))             # snps x indiv  (= Z^T in the GRM's sense)
+    ref.set_options(cores=cores, centered=False, variant=256)
+    h = ref.RefCompressed(plink, snps, indiv, f, indiv)
+    out = np.zeros((indiv, indiv), order="F")
+    ts = []
+    for it in range(3):
+        t0 = time.perf_counter()
+        h.dgemm("N", B, out)
+        if it >= 1:
+            ts.append(time.perf_counter() - t0)
+    h.free()
+    ref.set_options(cores=cores, centered=True, variant=256)
+    exact = bool(np.array_equal(out, (B.T @ B)))
+    t = sum(ts) / len(ts)
+    return {"value": 2.0 * indiv * indiv * snps / t / 1e12, "unit": "TOPS", "cores": cores,
+            "kind": "reference", "exact_counts": exact,
+            "sample": f"{snps} SNPs x {indiv} individuals, raw counts Z Z^T via reference CPU 5codes "
+                      f"dgemm_compressed('N', not centred) on B = Z^T, 2 calls after 1 warm-up, "
+                      f"{cores} threads; {t:.2f} s/call"}
 
 
 def main():
