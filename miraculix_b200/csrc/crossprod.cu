@@ -83,20 +83,38 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
 
   MB_CUDA(cudaEventRecord(e0, stream));
   // GRM: the row sums m = M 1 come exactly from the input, m = X (X^T 1) (64-bit integers), so
-  // the centring can be applied while the counts leave the accumulators.
+  // the centring can be applied while the counts leave the accumulators.  They are only needed
+  // by the epilogue of the LAST slab's GEMM, so they run on a side stream next to the expansion
+  // (both are small HBM/latency-bound kernels) and join right before that launch.
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  const bool overlap = mode == 1 && tc && !getenv("MB200_NO_ROWSUM_OVERLAP");
   if (mode == 1) {
+    if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+    cudaStream_t rs = stream;
+    if (overlap) {
+      MB_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+      MB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      MB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+      rs = side;
+    }
     MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
-    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, stream));
-    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
+    if (overlap) {
+      MB_CUDA(cudaEventRecord(ev_fork, stream));       // d_m, d_s allocated; caller's inputs ready
+      MB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    }
+    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, rs));
+    reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_m, rows, 0, d_m + rows);
     count_launch();
     if (do_scale) {
-      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
+      reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_f, k, 1, d_m + rows + 1);
       count_launch();
     }
     MB_LAUNCH_CHECK();
+    if (overlap) MB_CUDA(cudaEventRecord(ev_join, side));
   }
-  MB_CUDA(cudaEventRecord(e1, stream));  // [e0,e1) = row sums ("epilogue" time), [e1,e2) = GEMM
+  // [e0,e1) = row sums when they run in line (SIMT path), ~0 when overlapped; [e1,e2) = the rest
+  MB_CUDA(cudaEventRecord(e1, stream));
   CpFinish fin;
   fin.kind = 1;
   fin.affine = mode == 1;
@@ -116,6 +134,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     count_launch();
     MB_LAUNCH_CHECK();
     if (tc) {
+      if (overlap && slab == nslabs - 1) MB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
       MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
                                    sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, pair));
       executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
@@ -160,6 +179,9 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaEventDestroy(e2);
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  if (ev_join) cudaEventDestroy(ev_join);
+  if (side) cudaStreamDestroy(side);
   return 0;
 }
 

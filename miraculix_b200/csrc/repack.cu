@@ -107,17 +107,25 @@ constexpr int RF_TILE = 512;
 constexpr int RF_THREADS = 512;
 constexpr int RF_QP = 33;                       // words per (k, q) row of S
 constexpr int RF_KP = 32 * RF_QP + 1;           // words per k plane (+1: 4 rows of a warp hit 4 bank groups)
-constexpr int RF_SMEM = 16 * RF_KP * 4;         // 67648 bytes
+constexpr int RF_SMEM = 16 * RF_KP * 4 + RF_TILE * 4;   // 67648 bytes of tile + 2 KB of row counts
+static_assert(RF_THREADS == RF_TILE, "one row count per thread");
 
 __device__ __forceinline__ void transpose16x16_2bit(uint32_t (&a)[16]) {
+  // rounds 1 and 2 exchange whole bytes: one PRMT per output word instead of a 5-instruction
+  // delta swap (the kernel is issue/ALU-pipe bound, not HBM bound, once the loads are batched)
 #pragma unroll
   for (int k = 0; k < 8; k++) {   // fields 8..15 of word k <-> fields 0..7 of word k + 8
-    const uint32_t t = ((a[k] >> 16) ^ a[k + 8]) & 0x0000FFFFu;
-    a[k + 8] ^= t; a[k] ^= t << 16;
+    const uint32_t x = a[k], y = a[k + 8];
+    a[k] = __byte_perm(x, y, 0x5410);
+    a[k + 8] = __byte_perm(x, y, 0x7632);
   }
 #pragma unroll
   for (int k = 0; k < 16; k++)
-    if (!(k & 4)) { const uint32_t t = ((a[k] >> 8) ^ a[k + 4]) & 0x00FF00FFu; a[k + 4] ^= t; a[k] ^= t << 8; }
+    if (!(k & 4)) {               // bytes 1,3 of word k <-> bytes 0,2 of word k + 4
+      const uint32_t x = a[k], y = a[k + 4];
+      a[k] = __byte_perm(x, y, 0x6240);
+      a[k + 4] = __byte_perm(x, y, 0x7351);
+    }
 #pragma unroll
   for (int k = 0; k < 16; k++)
     if (!(k & 2)) { const uint32_t t = ((a[k] >> 4) ^ a[k + 2]) & 0x0F0F0F0Fu; a[k + 2] ^= t; a[k] ^= t << 4; }
@@ -131,6 +139,78 @@ template <> struct RfVec<1> { typedef uint32_t T; };
 template <> struct RfVec<2> { typedef uint2 T; };
 template <> struct RfVec<4> { typedef uint4 T; };
 
+// Phase 1 of the fast kernel: 32 / VW lanes per SNP row; read, recode, count, write SNP-major, stage
+// plain (un-interleaved) in smem.  The bed loads of a whole batch of rows are issued before the first
+// one is used: with one load in flight per thread the phase was a chain of NIT DRAM round trips
+// (ncu: 46 % of all stall samples on the first use of the loaded word).  After that fix the phase is
+// issue-bound, so everything per row is strength-reduced: running pointers instead of 64-bit
+// row * pitch products, constant smem offsets, row counts parked in smem (one coalesced atomic per
+// row after the barrier), and FULL = interior tile (no row / column / ragged-word predicates).
+template <int VW, bool FULL>
+__device__ __forceinline__ void rf_phase1(const uint32_t *__restrict__ plink, long s_begin, long s_count,
+                                          long indiv, long wpr, uint8_t *__restrict__ snp_major,
+                                          long pitch_s, long w0, long sl0, uint32_t *S, int *scnt,
+                                          int tid) {
+  typedef typename RfVec<VW>::T Vec;
+  constexpr int LPR = 32 / VW;                          // lanes per row
+  constexpr int RPI = RF_THREADS / LPR;                 // rows per iteration: 16 / 32 / 64
+  constexpr int NIT = RF_TILE / RPI;                    // iterations: 32 / 16 / 8
+  constexpr int BATCH = VW == 4 ? 4 : 8;                // loads in flight per thread (<= 16 registers)
+  constexpr int DST_STEP = (RPI / 16) * RF_QP;          // (r0 + i RPI) & 15 == r0 & 15, >> 4 grows by RPI / 16
+  const int wl = (tid % LPR) * VW;                      // first word of this thread in the segment
+  const long gw = w0 + wl;
+  const int r0 = tid / LPR;
+  const bool in_cols = FULL || gw < wpr;                // wpr % VW == 0: the vector is whole
+  const Vec *src = reinterpret_cast<const Vec *>(plink + (sl0 + r0) * wpr + gw);
+  const long src_step = (long)RPI * wpr / VW;
+  uint8_t *out = snp_major + (s_begin + sl0 + r0) * pitch_s + 4 * gw;
+  const long out_step = (long)RPI * pitch_s;
+  uint32_t *dst = S + (r0 & 15) * RF_KP + (r0 >> 4) * RF_QP + wl;
+  int *cdst = scnt + r0;
+  long rows_left = s_count - (sl0 + r0);                // row r of this thread exists iff rows_left > 0
+#pragma unroll 1
+  for (int it0 = 0; it0 < NIT; it0 += BATCH) {
+    union { Vec vec; uint32_t w[VW]; } raw[BATCH];      // Vec-aligned wherever the compiler keeps it
+#pragma unroll
+    for (int b = 0; b < BATCH; b++) {
+      if (FULL || (in_cols && rows_left > (long)b * RPI)) {
+        raw[b].vec = __ldg(src);
+      } else {
+#pragma unroll
+        for (int j = 0; j < VW; j++) raw[b].w[j] = 0;   // PLINK code 00 -> value 0
+      }
+      src += src_step;
+    }
+#pragma unroll
+    for (int b = 0; b < BATCH; b++) {
+      uint32_t v[VW];
+      union { Vec vec; uint32_t w[VW]; } o;
+      int cnt = 0;
+#pragma unroll
+      for (int j = 0; j < VW; j++) {
+        v[j] = plink_to_value_word(raw[b].w[j]);
+        if (!FULL) {
+          const long keep = indiv - 16 * (gw + j);      // valid fields in this word
+          if (keep < 16) v[j] = keep > 0 ? v[j] & ((1u << (2 * keep)) - 1u) : 0u;
+        }
+        cnt += __popc(v[j]) + __popc(v[j] & 0xAAAAAAAAu);   // sum of 2-bit values
+        o.w[j] = interleave_word(v[j]);
+      }
+      if (FULL || rows_left > (long)b * RPI)            // data, or row padding up to the 128-byte pitch
+        *reinterpret_cast<Vec *>(out) = o.vec;
+      out += out_step;
+#pragma unroll
+      for (int j = 0; j < VW; j++) dst[b * DST_STEP + j] = v[j];
+#pragma unroll
+      for (int o2 = LPR / 2; o2; o2 >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o2);
+      if ((tid % LPR) == 0) cdst[b * RPI] = cnt;
+    }
+    dst += BATCH * DST_STEP;
+    cdst += BATCH * RPI;
+    rows_left -= (long)BATCH * RPI;
+  }
+}
+
 // VW = words per thread in phase 1 (1, 2 or 4: what the alignment of the bed rows allows)
 template <int VW>
 __global__ void __launch_bounds__(RF_THREADS, 3)
@@ -139,55 +219,21 @@ repack_fast_kernel(const uint32_t *__restrict__ plink, long s_begin, long s_coun
                    long pitch_s, uint8_t *__restrict__ indiv_major, long pitch_i,
                    unsigned long long *__restrict__ counts) {
   extern __shared__ uint32_t S[];
-  typedef typename RfVec<VW>::T Vec;
+  int *scnt = reinterpret_cast<int *>(S + 16 * RF_KP);  // allele count of every SNP row of the tile
   const int tid = threadIdx.x, lane = tid & 31;
   const long w0 = (long)blockIdx.x * 32;                  // first word column (16 individuals each)
   const long sl0 = (long)blockIdx.y * RF_TILE;            // first SNP of the tile, chunk-local
   const bool edge = 16 * (w0 + 32) > indiv;               // tile holds the ragged end of the rows
 
-  // phase 1: 32 / VW lanes per SNP row; read, recode, count, write SNP-major, stage plain in smem
-  {
-    constexpr int LPR = 32 / VW;                          // lanes per row
-    constexpr int RPI = RF_THREADS / LPR;                 // rows per iteration
-    const int wl = (tid % LPR) * VW;                      // first word of this thread in the segment
-    const long gw = w0 + wl;
-#pragma unroll 2
-    for (int r = tid / LPR; r < RF_TILE; r += RPI) {
-      const long sl = sl0 + r;
-      uint32_t v[VW];
-#pragma unroll
-      for (int j = 0; j < VW; j++) v[j] = 0;
-      int cnt = 0;
-      const bool in_row = sl < s_count && gw < wpr;       // wpr % VW == 0: the vector is whole
-      if (in_row) {
-        const Vec raw = __ldg(reinterpret_cast<const Vec *>(plink + sl * wpr + gw));
-        const uint32_t *rw = reinterpret_cast<const uint32_t *>(&raw);
-        uint32_t o[VW];
-#pragma unroll
-        for (int j = 0; j < VW; j++) {
-          v[j] = plink_to_value_word(rw[j]);
-          if (edge) {
-            const long keep = indiv - 16 * (gw + j);      // valid fields in this word
-            if (keep < 16) v[j] = keep > 0 ? v[j] & ((1u << (2 * keep)) - 1u) : 0u;
-          }
-          cnt += __popc(v[j]) + __popc(v[j] & 0xAAAAAAAAu);   // sum of 2-bit values
-          o[j] = interleave_word(v[j]);
-        }
-        *reinterpret_cast<Vec *>(snp_major + (s_begin + sl) * pitch_s + 4 * gw) =
-            *reinterpret_cast<const Vec *>(o);
-      } else if (sl < s_count) {                          // row padding up to the 128-byte pitch
-        *reinterpret_cast<Vec *>(snp_major + (s_begin + sl) * pitch_s + 4 * gw) =
-            *reinterpret_cast<const Vec *>(v);
-      }
-      uint32_t *dst = S + (r & 15) * RF_KP + (r >> 4) * RF_QP + wl;
-#pragma unroll
-      for (int j = 0; j < VW; j++) dst[j] = v[j];
-#pragma unroll
-      for (int o2 = LPR / 2; o2; o2 >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o2);
-      if ((tid % LPR) == 0 && cnt) atomicAdd(&counts[s_begin + sl], (unsigned long long)cnt);
-    }
-  }
+  if (!edge && sl0 + RF_TILE <= s_count)
+    rf_phase1<VW, true>(plink, s_begin, s_count, indiv, wpr, snp_major, pitch_s, w0, sl0, S, scnt, tid);
+  else
+    rf_phase1<VW, false>(plink, s_begin, s_count, indiv, wpr, snp_major, pitch_s, w0, sl0, S, scnt, tid);
   __syncthreads();
+  {                                                       // RF_THREADS == RF_TILE: one row per thread
+    const int c = scnt[tid];
+    if (c && sl0 + tid < s_count) atomicAdd(&counts[s_begin + sl0 + tid], (unsigned long long)c);
+  }
 
   // phase 2: in-place transpose, two blocks per thread (block id = q * 32 + cw, lanes = cw).
   // SNP row k of a block is loaded into register 4 (k % 4) + k / 4, so the transposed word comes
