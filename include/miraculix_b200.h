@@ -120,8 +120,8 @@ int mb200_set_dgemm_mode(int mode, int slices);
  * Results do not depend on the chunking beyond fp64 summation order. */
 int mb200_set_pipeline(int chunks, double min_bytes);
 /* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct, one CTA per 128 x 256 tile,
- * 2 (default): tcgen05 cta_group::2, CTA pairs on 256 x 256 tiles (full-matrix products; the
- * partitioned GRM runs one CTA per tile). */
+ * 2 (default): tcgen05 cta_group::2, CTA pairs on 256 x 256 tiles (full-matrix products and the
+ * partitioned GRM, whose pairs take two consecutive row tiles of the partition). */
 int mb200_set_crossprod_mode(int mode);
 
 /* dgemm_compressed with DEVICE pointers dB, dC on the handle's device; asynchronous on the

@@ -236,13 +236,17 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   MB_CUDA(cudaEventCreate(&e2));
   MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
   const int nslabs = (int)ceil_div(nb, slab_kbytes);
-  if (nslabs > 1)  // int32 partials only exist when K needs several slabs
-    MB_CUDA(cudaMallocAsync(&C32, (size_t)local_rows * rows_pad * sizeof(int32_t), stream));
+  // mode 2: CTA pairs over this partition's consecutive row tiles (mi, mi + nparts)
+  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? nparts : 0;
+  if (nslabs > 1)  // int32 partials only exist when K needs several slabs (an odd tile count's
+                   // last pair has a phantom second half: rows padded to whole pairs)
+    MB_CUDA(cudaMallocAsync(&C32, (size_t)round_up(local_rows, 256) * rows_pad * sizeof(int32_t), stream));
   MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
   int real_tiles = 0;
   int num_tail = 0;
   const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
-  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb, sms, &num_tail, &real_tiles, 0));
+  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb,
+                           crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
 
   MB_CUDA(cudaEventRecord(e0, stream));
   if (mode == 1) {
@@ -280,7 +284,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     count_launch();
     MB_LAUNCH_CHECK();
     MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
-                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, 0));
+                                 slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, pair));
     executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
   }
   MB_CUDA(cudaEventRecord(e2, stream));

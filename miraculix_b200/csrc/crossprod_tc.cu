@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b,
                     const TileCoord *__restrict__ tiles, int num_tiles, int num_kblocks,
-                    int32_t *__restrict__ C32, long ld32, int accumulate, const CpFinish fin) {
+                    int32_t *__restrict__ C32, long ld32, int accumulate, const CpFinish fin,
+                    int mstride) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
@@ -62,9 +63,10 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * TC_STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // PAIR: the two CTAs of a cluster share one work item (a pair of row tiles mi, mi + 1 against
-  // column tile nj); rank 0 (the leader) issues the MMAs for both, every CTA loads its own operands
-  // and drains its own 128 accumulator rows.
+  // PAIR: the two CTAs of a cluster share one work item (a pair of row tiles mi, mi + mstride
+  // against column tile nj; mstride = 1, or the partition count when the row tiles of one GPU's
+  // panel are dealt cyclically); rank 0 (the leader) issues the MMAs for both, every CTA loads its
+  // own operands and drains its own 128 accumulator rows.
   const int rank = PAIR ? (int)cluster_ctarank() : 0;
   const int unit0 = PAIR ? blockIdx.x >> 1 : blockIdx.x, nunits = PAIR ? gridDim.x >> 1 : gridDim.x;
 
@@ -111,7 +113,7 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
             // serves the A tile and this CTA's half of the B tile
             if (rank == 0) mbar_expect_tx(&full[stage], 2 * TC_STAGE_BYTES);
             const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
-            tma_load_2d_pair(sa, &tmap_a, lead_full, kb * TC_BK, (tc.mi + rank) * TC_BM);
+            tma_load_2d_pair(sa, &tmap_a, lead_full, kb * TC_BK, (tc.mi + rank * mstride) * TC_BM);
             tma_load_2d_pair(sb, &tmap_a, lead_full, kb * TC_BK, tc.nj * TC_BN + rank * (TC_BN / 2));
           }
         }
@@ -174,10 +176,13 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int t = unit0; t < num_tiles; t += nunits) {
       TileCoord tc = tiles[t];
       if (PAIR) {  // this CTA's half of the pair
-        tc.mi += rank;
+        tc.mi += rank * mstride;
         tc.mo += rank;
         if (tc.slot >= 0) tc.slot = 2 * tc.slot + rank;
       }
+      // second half of a strided pair whose tile lies wholly left of the diagonal: computed by the
+      // 256-row MMA, not part of the result
+      const bool dead = PAIR && (long)TC_BN * (tc.nj + 1) <= (long)TC_BM * tc.mi;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const long row = (long)tc.mo * TC_BM + quad * 32 + lane;
@@ -189,7 +194,7 @@ crossprod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const bool iok = fin.kind && gi < fin.n;
       const long long ai = (fin.affine && iok) ? __double2ll_rn(fin.m[gi]) * aff.n : 0;
 #pragma unroll 1
-      for (int c = 0; c < TC_BN / 32; c++) {
+      for (int c = 0; c < TC_BN / 32 && !dead; c++) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr + c * 32, r);
         tmem_ld_wait();
@@ -322,6 +327,7 @@ __global__ void __launch_bounds__(256)
 tail_finish_kernel(const TileCoord *__restrict__ tail_tiles, const int *__restrict__ scratch,
                    const CpFinish fin) {
   const TileCoord tc = tail_tiles[blockIdx.x];
+  if ((long)TC_BN * (tc.nj + 1) <= (long)TC_BM * tc.mi) return;  // dead half of a strided pair
   const CpAffine aff = cp_affine_setup(fin.n, fin.affine, fin.do_scale, fin.scal);
   const int *src = scratch + (long)blockIdx.x * TC_BM * TC_BN;
   for (int e = threadIdx.x; e < TC_BM * TC_BN; e += 256) {
@@ -352,14 +358,16 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
   const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
   std::vector<TileCoord> v;
   if (pair) {
-    // work items = pairs of row tiles (2 Mi, 2 Mi + 1) against column tile nj >= Mi: both halves of
-    // such a pair are upper-triangle tiles (the operand is padded to a multiple of 256 rows)
-    if (nparts != 1) return fail(-2, __func__, __LINE__, "CTA-pair tiles are not partitioned");
+    // work items = pairs of this partition's consecutive row tiles (mi, mi + nparts) against column
+    // tile nj, listed when the first half touches the upper triangle.  nparts == 1: both halves of
+    // (2 Mi, 2 Mi + 1) are upper-triangle tiles for nj >= Mi.  nparts > 1: the second half may lie
+    // wholly left of the diagonal (at most nparts / 2 column tiles per pair; the epilogue drops it)
+    // or past the last row tile (odd tile count; TMA zero-fills, the epilogue's row guard drops it).
     for (int sn = 0; sn < Nt; sn += 8)
-      for (int sm = 0; sm < Mt; sm += 16)
+      for (int sm = 0; sm < Mt; sm += 16 * nparts)
         for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
-          for (int mi = sm; mi < sm + 16 && mi < Mt; mi += 2)
-            if (nj >= mi / 2) v.push_back({mi, nj, mi, 0, -1, -1});
+          for (int mi = sm + part; mi < sm + 16 * nparts && mi < Mt; mi += 2 * nparts)
+            if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi / nparts, 0, -1, -1});
   } else {
     for (int sn = 0; sn < Nt; sn += 8)
       for (int sm = 0; sm < Mt; sm += 16 * nparts)
@@ -387,7 +395,7 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
       *num_tiles = (int)v.size();
       for (const TileCoord &c : tail) {                  // finish list: one entry per scratch tile
         v.push_back(c);
-        if (pair) v.push_back({c.mi + 1, c.nj, c.mo + 1, 0, -1, -1});
+        if (pair) v.push_back({c.mi + nparts, c.nj, c.mo + 1, 0, -1, -1});
       }
     }
   }
@@ -433,6 +441,7 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         const TileCoord *d_tiles,
                         int num_tiles, int32_t *C32, long ld32, int accumulate, int sm_count,
                         cudaStream_t stream, const CpFinish *finish, int num_tail, int pair) {
+  // pair: 0 = one CTA per 128 x 256 tile; s >= 1 = CTA pairs over row tiles (mi, mi + s)
   CUtensorMap ta, tb;
   MB_CHECK(make_tmap_u8_2d(&ta, X8, kcols, rows_pad, pitch, TC_BK, TC_BM, 1));
   MB_CHECK(make_tmap_u8_2d(&tb, X8, kcols, rows_pad, pitch, TC_BK, TC_BN, 1));
@@ -463,13 +472,13 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
     cfg.attrs = &at;
     cfg.numAttrs = 1;
     MB_CUDA(cudaLaunchKernelEx(&cfg, crossprod_tc_kernel<true>, ta, tb, d_tiles, num_tiles,
-                               (int)(kcols / TC_BK), C32, ld32, accumulate, fin));
+                               (int)(kcols / TC_BK), C32, ld32, accumulate, fin, pair));
   } else {
     MB_CUDA(cudaFuncSetAttribute(crossprod_tc_kernel<false>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
     crossprod_tc_kernel<false><<<grid, TC_THREADS, TC_SMEM, stream>>>(ta, tb, d_tiles, num_tiles,
                                                                       (int)(kcols / TC_BK), C32, ld32,
-                                                                      accumulate, fin);
+                                                                      accumulate, fin, 1);
   }
   count_launch();
   MB_LAUNCH_CHECK();

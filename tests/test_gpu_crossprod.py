@@ -226,6 +226,45 @@ def test_grm_partition_with_k_slabs(gpu_lib, monkeypatch):
     assert relerr(panel[:128, :], want[rows[:128], :] * (np.arange(indiv)[None, :] >= 0)) <= TOL
 
 
+@pytest.mark.parametrize("snps,indiv,nparts", [(517, 1300, 2), (2100, 2900, 4), (300, 100, 2),
+                                               (9300, 3000, 2), (1200, 5100, 8)])
+def test_grm_partition_pairs_match_single_cta(gpu_lib, snps, indiv, nparts, monkeypatch):
+    """CTA-pair kernel on partition panels: a pair takes two consecutive row tiles of the partition
+    (mi, mi + nparts), so its second half can lie left of the diagonal (dropped) or past the last
+    row tile (odd tile count).  Panels must equal the one-CTA-per-tile panels bit for bit, counts
+    and centred GRM, single slab (with the K-split tail) and K slabs."""
+    from miraculix_b200 import api
+    _, Z, f = simulate.simulate(snps, indiv, seed=snps + indiv)
+    x = simulate.pack_2bit(Z)
+    for slab in (None, "0.002"):
+        if slab:
+            monkeypatch.setenv("MB200_SLAB_GB", slab)
+        try:
+            for mode in (0, 1):
+                for part in range(nparts):
+                    gpu_lib.mb200_set_crossprod_mode(1)
+                    try:
+                        r1, p1 = api.grm_partition(x, snps, indiv, part, nparts, mode=mode,
+                                                   do_scale=True, allele_freq=f)
+                    finally:
+                        gpu_lib.mb200_set_crossprod_mode(2)
+                    r2, p2 = api.grm_partition(x, snps, indiv, part, nparts, mode=mode, do_scale=True,
+                                               allele_freq=f)
+                    assert np.array_equal(r1, r2)
+                    assert np.array_equal(p1, p2), (mode, part, slab)
+        finally:
+            if slab:
+                monkeypatch.delenv("MB200_SLAB_GB")
+    if True:  # counts of the last partition against the exact integer product
+        rows, panel = api.grm_partition(x, snps, indiv, nparts - 1, nparts, mode=0)
+        want = exact_counts(Z)
+        for lr, i in enumerate(rows):
+            if i < indiv:
+                first = (i // 256) * 256
+                assert np.array_equal(panel[lr, first:], want[i, first:])
+                assert not panel[lr, :first].any()
+
+
 def test_k_split_tail_matches_unsplit(gpu_lib, monkeypatch):
     """Shape whose upper-triangle tile count (156) leaves a partial last round on 148 SMs: those
     tiles are cut along K into pieces (int32 partials in a scratch tile + tail_finish_kernel).
