@@ -24,6 +24,31 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         cudaStream_t stream, const CpFinish *finish, int num_tail, int pair);
 int crossprod_tc_units(int sm_count, int pair);
 
+// Side stream + fork/join events of the GRM row sums, created once per host thread and device:
+// creating them per call left the GPU idle for ~80 us between the call's first two events.
+struct SideStream {
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static int side_stream(int device, SideStream **out) {
+  static thread_local SideStream ss;
+  if (ss.device != device) {
+    if (ss.stream) {
+      cudaStreamDestroy(ss.stream);
+      cudaEventDestroy(ss.fork);
+      cudaEventDestroy(ss.join);
+      ss = SideStream();
+    }
+    MB_CUDA(cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking));
+    MB_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
+    MB_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+    ss.device = device;
+  }
+  *out = &ss;
+  return 0;
+}
+
 static int upload_lut() {
   uint8_t table[256];
   host_plink2twobit(table);
@@ -93,9 +118,11 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
     cudaStream_t rs = stream;
     if (overlap) {
-      MB_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-      MB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-      MB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+      SideStream *ss = nullptr;
+      MB_CHECK(side_stream(device, &ss));
+      side = ss->stream;
+      ev_fork = ss->fork;
+      ev_join = ss->join;
       rs = side;
     }
     MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
@@ -179,9 +206,6 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaEventDestroy(e2);
-  if (ev_fork) cudaEventDestroy(ev_fork);
-  if (ev_join) cudaEventDestroy(ev_join);
-  if (side) cudaStreamDestroy(side);
   return 0;
 }
 
