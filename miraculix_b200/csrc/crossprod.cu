@@ -49,6 +49,36 @@ static int side_stream(int device, SideStream **out) {
   return 0;
 }
 
+// GRM row sums m = M 1 (d_m[0..rows)), their total (d_m[rows]) and 2 sum f (1 - f) (d_m[rows + 1]),
+// exactly from the input: m = X (X^T 1) in 64-bit integers.  overlap: they run on the side stream,
+// forked from `stream` here (d_m, d_s allocated on it; the caller's inputs ready); the caller makes
+// `stream` wait on *join before the first kernel that reads d_m (the last slab's GEMM epilogue).
+static int grm_row_sums(const uint8_t *d_x, long rows, long nb, long k, int is_plink_format,
+                        const double *d_f, int do_scale, unsigned int *d_s, double *d_m, int device,
+                        cudaStream_t stream, bool overlap, cudaEvent_t *join) {
+  cudaStream_t rs = stream;
+  SideStream *ss = nullptr;
+  if (overlap) {
+    MB_CHECK(side_stream(device, &ss));
+    rs = ss->stream;
+    MB_CUDA(cudaEventRecord(ss->fork, stream));
+    MB_CUDA(cudaStreamWaitEvent(rs, ss->fork, 0));
+  }
+  MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, rs));
+  reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_m, rows, 0, d_m + rows);
+  count_launch();
+  if (do_scale) {
+    reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_f, k, 1, d_m + rows + 1);
+    count_launch();
+  }
+  MB_LAUNCH_CHECK();
+  if (overlap) {
+    MB_CUDA(cudaEventRecord(ss->join, rs));
+    *join = ss->join;
+  }
+  return 0;
+}
+
 static int upload_lut() {
   uint8_t table[256];
   host_plink2twobit(table);
@@ -111,34 +141,13 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   // the centring can be applied while the counts leave the accumulators.  They are only needed
   // by the epilogue of the LAST slab's GEMM, so they run on a side stream next to the expansion
   // (both are small HBM/latency-bound kernels) and join right before that launch.
-  cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_join = nullptr;
   const bool overlap = mode == 1 && tc && !getenv("MB200_NO_ROWSUM_OVERLAP");
   if (mode == 1) {
     if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-    cudaStream_t rs = stream;
-    if (overlap) {
-      SideStream *ss = nullptr;
-      MB_CHECK(side_stream(device, &ss));
-      side = ss->stream;
-      ev_fork = ss->fork;
-      ev_join = ss->join;
-      rs = side;
-    }
     MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
-    if (overlap) {
-      MB_CUDA(cudaEventRecord(ev_fork, stream));       // d_m, d_s allocated; caller's inputs ready
-      MB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
-    }
-    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, rs));
-    reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_m, rows, 0, d_m + rows);
-    count_launch();
-    if (do_scale) {
-      reduce_sum_kernel<<<1, 1024, 0, rs>>>(d_f, k, 1, d_m + rows + 1);
-      count_launch();
-    }
-    MB_LAUNCH_CHECK();
-    if (overlap) MB_CUDA(cudaEventRecord(ev_join, side));
+    MB_CHECK(grm_row_sums(d_x, rows, nb, k, is_plink_format, d_f, do_scale, d_s, d_m, device, stream,
+                          overlap, &ev_join));
   }
   // [e0,e1) = row sums when they run in line (SIMT path), ~0 when overlapped; [e1,e2) = the rest
   MB_CUDA(cudaEventRecord(e1, stream));
@@ -273,21 +282,17 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
                            crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
 
   MB_CUDA(cudaEventRecord(e0, stream));
+  cudaEvent_t ev_join = nullptr;
+  const bool overlap = mode == 1 && !getenv("MB200_NO_ROWSUM_OVERLAP");
   if (mode == 1) {
+    if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
     MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
-    MB_CHECK(input_row_sums(d_x, rows, nb, is_plink_format, d_s, d_m, stream));
-    reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_m, rows, 0, d_m + rows);
-    count_launch();
-    if (do_scale) {
-      if (!d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-      reduce_sum_kernel<<<1, 1024, 0, stream>>>(d_f, k, 1, d_m + rows + 1);
-      count_launch();
-    }
-    MB_LAUNCH_CHECK();
+    MB_CHECK(grm_row_sums(d_x, rows, nb, k, is_plink_format, d_f, do_scale, d_s, d_m, device, stream,
+                          overlap, &ev_join));
   }
   // entries left of a row tile's first computed column tile are not part of the panel: zero
   MB_CUDA(cudaMemsetAsync(d_panel, 0, sizeof(double) * (size_t)local_rows * rows, stream));
-  MB_CUDA(cudaEventRecord(e1, stream));  // [e0,e1) = row sums + panel clear, [e1,e2) = GEMM
+  MB_CUDA(cudaEventRecord(e1, stream));  // [e0,e1) = panel clear (+ in-line row sums), [e1,e2) = the rest
   CpFinish fin;
   fin.kind = 2;
   fin.affine = mode == 1;
@@ -307,6 +312,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
                                                    X8, rows_pad, kpad);
     count_launch();
     MB_LAUNCH_CHECK();
+    if (overlap && slab == nslabs - 1) MB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
     MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad,
                                  slab > 0, sms, stream, slab == nslabs - 1 ? &fin : nullptr, num_tail, pair));
     executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
