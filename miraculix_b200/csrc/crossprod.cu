@@ -24,6 +24,35 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
                         cudaStream_t stream, const CpFinish *finish, int num_tail, int pair);
 int crossprod_tc_units(int sm_count, int pair);
 
+// Stream-ordered scratch and timing events of one call: released on every exit path (an early
+// error return must not leak device memory of the retained pool).
+struct CallScratch {
+  cudaStream_t stream;
+  void *ptrs[8];
+  int n = 0;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  explicit CallScratch(cudaStream_t s) : stream(s) {}
+  template <typename T> cudaError_t alloc(T **p, size_t bytes) {
+    void *q = nullptr;
+    const cudaError_t e = n < 8 ? cudaMallocAsync(&q, bytes, stream) : cudaErrorMemoryAllocation;
+    if (e == cudaSuccess) ptrs[n++] = q;
+    *p = static_cast<T *>(q);
+    return e;
+  }
+  void adopt(void *p) { if (p && n < 8) ptrs[n++] = p; }
+  cudaError_t events() {
+    for (int i = 0; i < 3; i++) {
+      const cudaError_t e = cudaEventCreate(&ev[i]);
+      if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+  }
+  ~CallScratch() {
+    for (int i = 0; i < n; i++) cudaFreeAsync(ptrs[i], stream);
+    for (int i = 0; i < 3; i++) if (ev[i]) cudaEventDestroy(ev[i]);
+  }
+};
+
 // Side stream + fork/join events of the GRM row sums, created once per host thread and device:
 // creating them per call left the GPU idle for ~80 us between the call's first two events.
 struct SideStream {
@@ -123,18 +152,20 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   // tensor-core path: the last slab's GEMM epilogue writes the final fp64 matrix itself (counts,
   // or the centred/scaled GRM), so the int32 matrix only exists when K needs several slabs
   const bool need_c32 = !tc || nslabs > 1;
-  cudaEvent_t e0, e1, e2;
-  MB_CUDA(cudaEventCreate(&e0));
-  MB_CUDA(cudaEventCreate(&e1));
-  MB_CUDA(cudaEventCreate(&e2));
-  MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
-  if (need_c32) MB_CUDA(cudaMallocAsync(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t), stream));
-  MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
+  CallScratch scratch(stream);
+  MB_CUDA(scratch.events());
+  const cudaEvent_t e0 = scratch.ev[0], e1 = scratch.ev[1], e2 = scratch.ev[2];
+  MB_CUDA(scratch.alloc(&X8, (size_t)rows_pad * kpad));
+  if (need_c32) MB_CUDA(scratch.alloc(&C32, (size_t)rows_pad * rows_pad * sizeof(int32_t)));
+  MB_CUDA(scratch.alloc(&d_m, sizeof(double) * (rows + 8)));
   int real_tiles = 0;
   int num_tail = 0;  // single slab: the last partial round of tiles is cut along K (crossprod_tc.cu)
   const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
-  if (tc) MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream, split_kb,
-                                   crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
+  if (tc) {
+    MB_CHECK(build_tile_list(rows, 0, 1, &d_tiles, &num_tiles, stream, split_kb,
+                             crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
+    scratch.adopt(d_tiles);
+  }
 
   MB_CUDA(cudaEventRecord(e0, stream));
   // GRM: the row sums m = M 1 come exactly from the input, m = X (X^T 1) (64-bit integers), so
@@ -142,10 +173,12 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   // by the epilogue of the LAST slab's GEMM, so they run on a side stream next to the expansion
   // (both are small HBM/latency-bound kernels) and join right before that launch.
   cudaEvent_t ev_join = nullptr;
-  const bool overlap = mode == 1 && tc && !getenv("MB200_NO_ROWSUM_OVERLAP");
+  // (single slab only: next to the GEMMs of earlier slabs they cost more than they hide -- measured
+  // at configs[4], +8..18 ms on 400)
+  const bool overlap = mode == 1 && tc && nslabs == 1 && !getenv("MB200_NO_ROWSUM_OVERLAP");
   if (mode == 1) {
     if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
+    MB_CUDA(scratch.alloc(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb)));
     MB_CHECK(grm_row_sums(d_x, rows, nb, k, is_plink_format, d_f, do_scale, d_s, d_m, device, stream,
                           overlap, &ev_join));
   }
@@ -165,8 +198,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
     const long kuse = round_up(kbytes * 4, 128);  // columns the GEMM walks this slab
     // expand zero-fills the whole pitch beyond this slab's bytes; the GEMM walks [0, kuse)
-    expand_2bit_kernel<<<sms * 8, 256, 0, stream>>>(d_x, rows, nb, kb0, kbytes, is_plink_format,
-                                                   X8, rows_pad, kpad);
+    expand_2bit_launch(d_x, rows, nb, kb0, kbytes, is_plink_format, X8, rows_pad, kpad, sms, stream);
     count_launch();
     MB_LAUNCH_CHECK();
     if (tc) {
@@ -198,12 +230,7 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
   }
   MB_CUDA(cudaEventRecord(e2, stream));
 
-  MB_CUDA(cudaFreeAsync(X8, stream));
-  if (C32) MB_CUDA(cudaFreeAsync(C32, stream));
-  MB_CUDA(cudaFreeAsync(d_m, stream));
-  if (d_s) MB_CUDA(cudaFreeAsync(d_s, stream));
-  if (d_tiles) MB_CUDA(cudaFreeAsync(d_tiles, stream));
-  MB_CUDA(cudaStreamSynchronize(stream));
+  MB_CUDA(cudaStreamSynchronize(stream));  // scratch goes back to the pool when `scratch` leaves scope
   if (timing) {
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);
@@ -212,9 +239,6 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
     timing->epilogue_ms = a;  // row sums from the input (GRM only)
     timing->executed_ops = executed_ops;
   }
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
-  cudaEventDestroy(e2);
   return 0;
 }
 
@@ -263,30 +287,30 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   unsigned int *d_s = nullptr;
   TileCoord *d_tiles = nullptr;
   int num_tiles = 0;
-  cudaEvent_t e0, e1, e2;
-  MB_CUDA(cudaEventCreate(&e0));
-  MB_CUDA(cudaEventCreate(&e1));
-  MB_CUDA(cudaEventCreate(&e2));
-  MB_CUDA(cudaMallocAsync(&X8, (size_t)rows_pad * kpad, stream));
+  CallScratch scratch(stream);
+  MB_CUDA(scratch.events());
+  const cudaEvent_t e0 = scratch.ev[0], e1 = scratch.ev[1], e2 = scratch.ev[2];
+  MB_CUDA(scratch.alloc(&X8, (size_t)rows_pad * kpad));
   const int nslabs = (int)ceil_div(nb, slab_kbytes);
   // mode 2: CTA pairs over this partition's consecutive row tiles (mi, mi + nparts)
   const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? nparts : 0;
   if (nslabs > 1)  // int32 partials only exist when K needs several slabs (an odd tile count's
                    // last pair has a phantom second half: rows padded to whole pairs)
-    MB_CUDA(cudaMallocAsync(&C32, (size_t)round_up(local_rows, 256) * rows_pad * sizeof(int32_t), stream));
-  MB_CUDA(cudaMallocAsync(&d_m, sizeof(double) * (rows + 8), stream));
+    MB_CUDA(scratch.alloc(&C32, (size_t)round_up(local_rows, 256) * rows_pad * sizeof(int32_t)));
+  MB_CUDA(scratch.alloc(&d_m, sizeof(double) * (rows + 8)));
   int real_tiles = 0;
   int num_tail = 0;
   const int split_kb = nslabs == 1 && !getenv("MB200_NO_TAIL_SPLIT") ? (int)(round_up(nb * 4, 128) / 128) : 0;
   MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, split_kb,
                            crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
+  scratch.adopt(d_tiles);
 
   MB_CUDA(cudaEventRecord(e0, stream));
   cudaEvent_t ev_join = nullptr;
-  const bool overlap = mode == 1 && !getenv("MB200_NO_ROWSUM_OVERLAP");
+  const bool overlap = mode == 1 && nslabs == 1 && !getenv("MB200_NO_ROWSUM_OVERLAP");  // see crossprod_device
   if (mode == 1) {
     if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
-    MB_CUDA(cudaMallocAsync(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb), stream));
+    MB_CUDA(scratch.alloc(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb)));
     MB_CHECK(grm_row_sums(d_x, rows, nb, k, is_plink_format, d_f, do_scale, d_s, d_m, device, stream,
                           overlap, &ev_join));
   }
@@ -308,8 +332,7 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
     const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
     const long kuse = round_up(kbytes * 4, 128);
-    expand_2bit_kernel<<<sms * 8, 256, 0, stream>>>(d_x, rows, nb, kb0, kbytes, is_plink_format,
-                                                   X8, rows_pad, kpad);
+    expand_2bit_launch(d_x, rows, nb, kb0, kbytes, is_plink_format, X8, rows_pad, kpad, sms, stream);
     count_launch();
     MB_LAUNCH_CHECK();
     if (overlap && slab == nslabs - 1) MB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
@@ -319,11 +342,6 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
   }
   MB_CUDA(cudaEventRecord(e2, stream));
 
-  MB_CUDA(cudaFreeAsync(X8, stream));
-  if (C32) MB_CUDA(cudaFreeAsync(C32, stream));
-  MB_CUDA(cudaFreeAsync(d_m, stream));
-  if (d_s) MB_CUDA(cudaFreeAsync(d_s, stream));
-  MB_CUDA(cudaFreeAsync(d_tiles, stream));
   MB_CUDA(cudaStreamSynchronize(stream));
   if (timing) {
     float a = 0, b = 0;
@@ -333,9 +351,6 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     timing->epilogue_ms = a;
     timing->executed_ops = executed_ops;
   }
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
-  cudaEventDestroy(e2);
   return 0;
 }
 

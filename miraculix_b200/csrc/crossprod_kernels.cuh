@@ -1,6 +1,7 @@
 // crossprod_kernels.cuh -- small HBM-bound kernels around the crossproduct GEMM
 // (SURVEY.md 8a rows a9, a11, a12, a13).
 #pragma once
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace mb200 {
@@ -51,6 +52,56 @@ expand_2bit_kernel(const uint8_t *__restrict__ x, long rows, long nb, long kb0, 
       }
     }
     *reinterpret_cast<uint4 *>(X8 + r * kpad + gc * 16) = make_uint4(out[0], out[1], out[2], out[3]);
+  }
+}
+
+// Word path of the expansion (the code IS the value: not PLINK-coded; rows and slab start whole
+// 32-bit words): one 4-byte load and one 16-byte store per thread, four rows in flight, no 64-bit
+// divisions -- the byte kernel above was issue bound (68 % issue slots, 44 % of DRAM peak).
+// grid.x covers the 16-byte groups of a row, grid.y strides over the rows.
+__global__ void __launch_bounds__(256)
+expand_2bit_words_kernel(const uint32_t *__restrict__ x, long rows, long nw, long kw0, long kbytes,
+                         int8_t *__restrict__ X8, long rows_pad, long kpad) {
+  const long gc = (long)blockIdx.x * blockDim.x + threadIdx.x;   // packed word of the slab
+  if (gc >= kpad / 16) return;
+  const long left = kbytes - 4 * gc;                             // packed bytes of this word inside the slab
+  const uint32_t keep = left >= 4 ? 0xFFFFFFFFu : left > 0 ? (1u << (8 * left)) - 1u : 0u;
+  const uint32_t *src = x + kw0 + gc;
+  uint4 *dst = reinterpret_cast<uint4 *>(X8 + gc * 16);
+  const long pitch4 = kpad / 16;
+  for (long r0 = (long)blockIdx.y * 4; r0 < rows_pad; r0 += (long)gridDim.y * 4) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) w[i] = (keep && r0 + i < rows) ? __ldg(src + (r0 + i) * nw) & keep : 0u;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      if (r0 + i >= rows_pad) break;
+      uint32_t o[4];
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const uint32_t v = __byte_perm(w[i], 0u, 0x4440 + t);    // byte t, zero-extended
+        o[t] = (v | (v << 6) | (v << 12) | (v << 18)) & 0x03030303u;
+      }
+      dst[(r0 + i) * pitch4] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// Launches the expansion of one K-slab (word path when the layout allows it).
+inline void expand_2bit_launch(const uint8_t *d_x, long rows, long nb, long kb0, long kbytes,
+                               int is_plink, int8_t *X8, long rows_pad, long kpad, int sms,
+                               cudaStream_t stream) {
+  static const bool bytes_only = getenv("MB200_EXPAND_BYTES") != nullptr;  // A/B switch
+  if (!bytes_only && !is_plink && nb % 4 == 0 && kb0 % 4 == 0 && (reinterpret_cast<uintptr_t>(d_x) & 3) == 0) {
+    const unsigned gx = (unsigned)ceil_div(kpad / 16, 256);
+    long gy = ceil_div((long)sms * 16, (long)gx);                // ~16 blocks per SM in flight
+    if (gy > ceil_div(rows_pad, 4)) gy = ceil_div(rows_pad, 4);
+    if (gy > 65535) gy = 65535;
+    expand_2bit_words_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(
+        reinterpret_cast<const uint32_t *>(d_x), rows, nb / 4, kb0 / 4, kbytes, X8, rows_pad, kpad);
+  } else {
+    expand_2bit_kernel<<<sms * 8, 256, 0, stream>>>(d_x, rows, nb, kb0, kbytes, is_plink, X8, rows_pad,
+                                                    kpad);
   }
 }
 

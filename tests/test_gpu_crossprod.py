@@ -29,7 +29,7 @@ def exact_counts(vals):
 
 @pytest.mark.parametrize("mode", [0, 1, 2])
 @pytest.mark.parametrize("snps,indiv", [(953, 752), (64, 5), (129, 257), (2051, 1343),
-                                        (10251, 5343)])
+                                        (10251, 5343), (1024, 515), (8176, 1030)])
 def test_counts_bit_exact(gpu_lib, snps, indiv, mode):
     from miraculix_b200 import api
     if mode == 0 and snps * indiv > 4e6:
