@@ -261,8 +261,8 @@ def grm_partition(x: np.ndarray, snps: int, indiv: int, part: int, nparts: int, 
                                      f.ctypes.data if f is not None else None, do_scale, part, nparts,
                                      panel.ctypes.data)
         _check(rc, "mb200_grm_partition")
-    lr = np.arange(lrows)
-    return ((lr // 128) * nparts + part) * 128 + lr % 128, panel
+    from .sharded import partition_tile_rows
+    return partition_tile_rows(indiv, part, nparts), panel
 
 
 def dense_solve(M: np.ndarray, B: np.ndarray, calc_logdet: bool = False, oversubscribe: bool = False):

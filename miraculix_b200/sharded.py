@@ -37,6 +37,49 @@ def partition_snps(snps: int, world: int) -> List[Tuple[int, int]]:
     return out
 
 
+TILE = 128  # rows per output tile of the crossproduct partition (csrc/crossprod.cu)
+
+
+def partition_tile_rows(rows: int, part: int, nparts: int):
+    """Global row index of every local row of partition `part` of `nparts` of the 2-D output-tile
+    partition of the GRM (include/miraculix_b200.h, mb200_crossprod_partition_device): the
+    partition owns the 128-row tiles t with t % nparts == part; indices >= rows are the padding of
+    the last tile.  Same length as mb200_crossprod_partition_rows(rows, part, nparts)."""
+    import numpy as np
+    if rows < 0 or nparts < 1 or not 0 <= part < nparts:
+        raise ValueError("rows >= 0 and 0 <= part < nparts required")
+    tiles = (rows + TILE - 1) // TILE
+    owned = (tiles - part + nparts - 1) // nparts if part < tiles else 0
+    lr = np.arange(owned * TILE, dtype=np.int64)
+    return ((lr // TILE) * nparts + part) * TILE + lr % TILE
+
+
+def assemble_grm_panels(panels, rows: int):
+    """Full symmetric rows x rows matrix from the panels of ALL partitions (panels[part] =
+    [local_rows][rows], row-major, as mb200_crossprod_partition_device writes them).  A panel row
+    holds global row i from column 256 floor(i/256) on; the rest comes from symmetry -- the
+    reference fills the lower triangle the same way (crossproduct.jl:100-106)."""
+    import numpy as np
+    nparts = len(panels)
+    out = np.zeros((rows, rows), dtype=np.float64)
+    seen = np.zeros(rows, dtype=bool)
+    for part, panel in enumerate(panels):
+        idx = partition_tile_rows(rows, part, nparts)
+        panel = np.asarray(panel)
+        if panel.shape != (idx.size, rows):
+            raise ValueError(f"panel {part}: shape {panel.shape}, expected {(idx.size, rows)}")
+        for lr in np.flatnonzero(idx < rows):
+            i = int(idx[lr])
+            first = (i // 256) * 256
+            out[i, first:] = panel[lr, first:]
+            seen[i] = True
+    if not seen.all():
+        raise ValueError("panels do not cover every row")
+    iu = np.triu_indices(rows, 1)
+    out.T[iu] = out[iu]
+    return out
+
+
 class ShardedCompressed:
     """Rank-local view of a SNP-block-sharded compressed matrix.
 

@@ -200,6 +200,24 @@ def test_grm_partition_assembles_to_full(gpu_lib, snps, indiv, nparts):
         assert np.array_equal(got[iu], full[iu]), mode
 
 
+@pytest.mark.parametrize("snps,indiv,nparts", [(1003, 700, 3), (515, 1300, 2)])
+def test_grm_partition_host_assembly(gpu_lib, snps, indiv, nparts):
+    """sharded.assemble_grm_panels over the device panels == the single-GPU GRM, bit for bit, and
+    == the oracle within the fp64 tolerance of north_star (1e-10 relative)."""
+    from miraculix_b200 import api
+    from miraculix_b200.sharded import assemble_grm_panels
+    plink, Z, f = simulate.simulate(snps, indiv, seed=7 * snps + nparts)
+    x = simulate.pack_2bit(Z)
+    full = api.grm(x, snps, indiv, do_scale=True, allele_freq=f)
+    panels = [api.grm_partition(x, snps, indiv, p, nparts, mode=1, do_scale=True, allele_freq=f)[1]
+              for p in range(nparts)]
+    got = assemble_grm_panels(panels, indiv)
+    iu = np.triu_indices(indiv)
+    assert np.array_equal(got[iu], full[iu])
+    assert np.array_equal(got, got.T)
+    assert relerr(got, cport.grm_epilogue(cport.crossprod(x, snps, indiv), f, True)) <= TOL
+
+
 def test_grm_partition_with_k_slabs(gpu_lib, monkeypatch):
     """The configs[4] schedule (1M SNPs: the int8 expansion does not fit, K goes in slabs with int32
     partials per partition, the fused epilogue runs on the last slab) at test size: panels of a

@@ -81,3 +81,68 @@ def test_world2_gloo_matches_unsharded():
         assert p.exitcode == 0
     en, et = out.get(timeout=10)
     assert en <= 1e-12 and et <= 1e-12, (en, et)
+
+
+def test_grm_tile_partition_rules():
+    """Host rule of the 2-D output-tile partition: every row owned exactly once, row counts agree
+    with the library's mb200_crossprod_partition_rows (a host-only query, no GPU needed)."""
+    from miraculix_b200 import api
+    from miraculix_b200.sharded import TILE, partition_tile_rows
+    lib = api.load_library()
+    for rows, nparts in [(100_000, 8), (10_000, 1), (10_000, 3), (700, 3), (128, 2), (1, 4), (257, 8)]:
+        owned = []
+        for part in range(nparts):
+            idx = partition_tile_rows(rows, part, nparts)
+            assert idx.size == lib.mb200_crossprod_partition_rows(rows, part, nparts)
+            assert idx.size % TILE == 0
+            assert (np.diff(idx) > 0).all()
+            owned.append(idx[idx < rows])
+        owned = np.sort(np.concatenate(owned))
+        assert np.array_equal(owned, np.arange(rows))
+        sizes = [partition_tile_rows(rows, p, nparts).size for p in range(nparts)]
+        assert max(sizes) - min(sizes) <= TILE  # balanced to one tile
+    with pytest.raises(ValueError):
+        partition_tile_rows(10, 2, 2)
+
+
+def _grm_worker(rank, world, port, snps, indiv, out):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from miraculix_b200.sharded import assemble_grm_panels, partition_tile_rows
+    from oracle import cport, simulate
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    plink, Z, f = simulate.simulate(snps, indiv, seed=11)
+    x = simulate.pack_2bit(Z)
+    # the oracle as the rank-local product: this rank's rows of the centred GRM, written the way
+    # mb200_crossprod_partition_device writes a panel (zeros left of the diagonal 256-tile)
+    full = cport.grm_epilogue(cport.crossprod(x, snps, indiv), f, True)
+    idx = partition_tile_rows(indiv, rank, world)
+    panel = np.zeros((idx.size, indiv))
+    for lr, i in enumerate(idx):
+        if i < indiv:
+            first = (i // 256) * 256
+            panel[lr, first:] = full[i, first:]
+    gathered = [None] * world
+    dist.all_gather_object(gathered, panel)  # the only exchange: collecting the finished panels
+    if rank == 0:
+        got = assemble_grm_panels(gathered, indiv)
+        out.put(bool(np.array_equal(got, full)) and bool(np.array_equal(got, got.T)))
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_grm_panels_assemble():
+    """configs[4]'s partition on two ranks: panels assemble to the unsharded GRM bit for bit."""
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    procs = [ctx.Process(target=_grm_worker, args=(r, 2, port, 301, 700, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+        assert p.exitcode == 0
+    assert out.get(timeout=10)
