@@ -91,3 +91,23 @@ def test_no_device_fails_loudly(lib):
         api.init_compressed(plink, 4, 4, np.zeros(4), 1)
     with pytest.raises(api.MiraculixError):
         api.snp_crossprod(np.zeros((4, 1), np.uint8), 4, 4, is_snpmajor=False)
+
+
+def test_product_never_touches_the_oracle(lib):
+    """The oracle is test infrastructure: nothing under miraculix_b200/ imports, opens or links it,
+    and the shipped library depends on neither the oracle's nor the reference's shared object."""
+    pkg = os.path.join(ROOT, "miraculix_b200")
+    pat = re.compile(r"^\s*(from|import)\s+oracle\b|oracle/|oracle\.|_ref\b|ref_miraculix", re.M)
+    for base, _, files in os.walk(pkg):
+        for name in files:
+            if not name.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                continue
+            src = open(os.path.join(base, name)).read()
+            src = re.sub(r'""".*?"""', "", src, flags=re.S)  # docstrings may mention the tests
+            assert not pat.search(src), f"{name} refers to the oracle"
+    from miraculix_b200 import api
+    out = subprocess.run(["ldd", api.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "ref_miraculix" not in out
+    mods = _run("import sys, miraculix_b200, miraculix_b200.api, miraculix_b200.sharded;"
+                "print([m for m in sys.modules if m.split('.')[0] == 'oracle'])")
+    assert mods.returncode == 0 and mods.stdout.strip() == "[]", mods.stdout + mods.stderr
