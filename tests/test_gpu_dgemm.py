@@ -173,7 +173,7 @@ def test_dgemm_linearity_and_transpose_identity_large(gpu_lib):
         assert relerr(a12, 2.0 * a1 - 3.0 * a2) <= 1e-9
         u = rng.standard_normal((indiv, 1))
         atu = api.dgemm_compressed("T", h, u, snps, indiv)
-        lhs, rhs = float(u.T @ a1), float(atu.T @ v1)
+        lhs, rhs = (u.T @ a1).item(), (atu.T @ v1).item()
         assert abs(lhs - rhs) <= 1e-9 * max(abs(lhs), np.linalg.norm(u) * np.linalg.norm(a1))
         # two columns at once == two single calls
         both = api.dgemm_compressed("N", h, np.hstack([v1, v2]), snps, indiv)
