@@ -77,7 +77,7 @@ class ClockSampler(threading.Thread):
     def run(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-             "clocks_event_reasons.sw_power_cap")
+             "clocks_event_reasons.sw_power_cap,power.draw")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -87,17 +87,32 @@ class ClockSampler(threading.Thread):
         except Exception:
             pass
 
+    def mark(self):
+        """Number of samples taken so far (to split the record into phases)."""
+        return len(self.rows)
+
     def stop(self):
         if self.proc:
             self.proc.terminate()
         self.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        return self.stats(self.rows)
+
+    @staticmethod
+    def stats(rows):
+        sm = [float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4)
+        reasons = sorted({names[i] for r in rows if len(r) >= 6 for i in range(4)
                           if r[2 + i].lower().startswith("active")})
+        pw = []
+        for r in rows:
+            try:
+                pw.append(float(r[6]))
+            except (IndexError, ValueError):
+                pass
         return {"sm_mhz": statistics.median(sm) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm),
+                "power_w": statistics.median(pw) if pw else None}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -255,7 +270,9 @@ def run_ours(args):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
+    mark0 = sampler.mark() if sampler else 0
     total_ms, launches = timed(step_device, args.steps, args.warmup)
+    mark1 = sampler.mark() if sampler else 0
     # per-launch durations of the dominant kernel inside the timed region (event ring)
     nlast = min(2 * args.steps, 128)
     ms_arr = (C.c_float * nlast)()
@@ -284,7 +301,11 @@ def run_ours(args):
     e2e_ms, _ = timed(step_e2e, e2e_steps, 1)
     if world == 1 and lib.mb200_last_status() != 0:
         raise SystemExit("dgemm_compressed failed: " + lib.mb200_last_message().decode())
-    clocks = sampler.stop() if sampler else None
+    clocks = None
+    if sampler:
+        sampler.stop()
+        clocks = ClockSampler.stats(sampler.rows)               # whole run: device-timed + e2e legs
+        clocks["device_timed"] = ClockSampler.stats(sampler.rows[mark0:mark1])
     pcg = None
     if not args.no_pcg:
         pcg = run_pcg(args, lib, api, dev, rank, world)

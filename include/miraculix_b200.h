@@ -99,8 +99,43 @@ void dgemm_plink(char *trans, char *plink, char *plink_transposed, int snps, int
                  int n, double *B, int Ldb, double *C, int Ldc);
 
 /* ------------------------------------------------------------------------------------------
+ * Several GPUs behind the SAME calls (the reference is single-device and selects it
+ * with CUDA_DEVICE, src/cuda/cuda_utils.cu:188-248).  Environment, read when a handle is created
+ * or a crossproduct is called:
+ *   MIRACULIX_NGPUS=N     shard over devices CUDA_DEVICE .. CUDA_DEVICE+N-1 (CUDA_DEVICE default 0)
+ *   CUDA_DEVICE=0,2,5     shard over an explicit list
+ *   TILE_SIZE=rows        crossproduct: cap on the row height of the int32 accumulation panel a
+ *                         device holds per pass (the reference's memory knob,
+ *                         src/cuda/snp_multiply_cuda.cu:68-72); MB200_GRM_ACC_GB caps its bytes
+ *   PRINT_LEVEL           >= 0: banner + one line per call, > 0: per-call details (cuda_utils.cu:44-82)
+ * plink2compressed then returns ONE handle for the whole matrix, sharded by 512-SNP blocks: one
+ * host thread per device inside the library, 'T' all-gathers the replicated B over NVLink (every
+ * device uploads 1/N of it), 'N' reduce-scatters the partial C (every device downloads 1/N), the
+ * CG exchanges indiv doubles per product -- all with the library's own peer-memory kernels, one
+ * process, no NCCL.  snp_multiply_gpu / mb200_grm split the output row tiles over the devices and
+ * stream panels straight into `ans`.  Unchanged single-process callers (Julia ccall, Fortran
+ * bind(C)) therefore use all GPUs.  Caller memory may be pageable: it is staged through pinned
+ * rings inside the library, so the copy/compute overlap does not depend on page-locked buffers.
+ * ---------------------------------------------------------------------------------------- */
+
+/* ------------------------------------------------------------------------------------------
  * PART 2 -- additive entry points (not in the reference)
  * ---------------------------------------------------------------------------------------- */
+
+/* Programmatic form of MIRACULIX_NGPUS / CUDA_DEVICE=a,b,c for the handles and crossproducts
+ * created afterwards; n <= 0 returns to the environment.  A device may be listed more than once
+ * (its shards then share the GPU -- exercises the multi-device path on a one-GPU box). */
+int mb200_set_devices(int n, const int *devices);
+/* Number of device shards behind a handle (1 for an ordinary handle), and shard g as an ordinary
+ * single-device handle (owned by the parent; valid for mb200_get_layout / mb200_download_layout /
+ * the device-pointer calls) with its SNP range [snp_begin, snp_begin + snp_count). */
+int mb200_shard_count(void *compressed);
+int mb200_get_shard(void *compressed, int g, void **shard, long *snp_begin, long *snp_count);
+/* Handle whose genotypes come from the on-device simulator below (same law and seed rule: the
+ * matrix depends on (seed, snps, indiv) only, not on the number of devices); f = allele counts /
+ * (2 indiv).  For benchmarks and scale tests: the bed never exists on the host. */
+int mb200_simulate_compressed(long snps, long indiv, unsigned long long seed, int max_n,
+                              void **compressed);
 
 /* Status of the last call on this thread: 0 ok, else cudaError / internal code; message text. */
 int mb200_last_status(void);

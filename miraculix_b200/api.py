@@ -81,6 +81,12 @@ SIGNATURES = {
     "mb200_cg_solve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                         C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int),
                                         C.POINTER(C.c_double)]),
+    "mb200_set_devices": (C.c_int, [C.c_int, C.POINTER(C.c_int)]),
+    "mb200_shard_count": (C.c_int, [C.c_void_p]),
+    "mb200_get_shard": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_long),
+                                  C.POINTER(C.c_long)]),
+    "mb200_simulate_compressed": (C.c_int, [C.c_long, C.c_long, C.c_ulonglong, C.c_int,
+                                            C.POINTER(C.c_void_p)]),
     "mb200_cg_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int,
                                  C.POINTER(C.c_int), C.POINTER(C.c_double)]),
 }
@@ -169,6 +175,33 @@ def dgemm_compressed(trans: str, handle: C.c_void_p, B: np.ndarray, snps: int, i
     lib.dgemm_compressed(trans.encode()[:1], handle, n, B.ctypes.data, k, out.ctypes.data, m)
     _check(lib.mb200_last_status(), "dgemm_compressed")
     return out
+
+
+def set_devices(devices=None) -> None:
+    """Devices the next handles / crossproducts use (MIRACULIX_NGPUS / CUDA_DEVICE=a,b,c in code);
+    None or [] = back to the environment."""
+    devices = list(devices or [])
+    arr = (C.c_int * max(1, len(devices)))(*devices)
+    _check(load_library().mb200_set_devices(len(devices), arr), "mb200_set_devices")
+
+
+def shards(handle: C.c_void_p):
+    """[(shard_handle, snp_begin, snp_count)] of a (possibly multi-device) handle."""
+    lib = load_library()
+    out = []
+    for g in range(lib.mb200_shard_count(handle)):
+        sh, b, c = C.c_void_p(None), C.c_long(0), C.c_long(0)
+        _check(lib.mb200_get_shard(handle, g, C.byref(sh), C.byref(b), C.byref(c)), "mb200_get_shard")
+        out.append((sh, b.value, c.value))
+    return out
+
+
+def simulate_compressed(snps: int, indiv: int, seed: int, max_ncol: int) -> C.c_void_p:
+    """Handle from the on-device simulator (one device, or sharded per set_devices / environment)."""
+    h = C.c_void_p(None)
+    _check(load_library().mb200_simulate_compressed(snps, indiv, seed, max_ncol, C.byref(h)),
+           "mb200_simulate_compressed")
+    return h
 
 
 def free_compressed(handle: C.c_void_p) -> None:

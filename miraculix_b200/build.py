@@ -11,10 +11,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmiraculix_b200.so")
-SOURCES = ["abi.cu", "repack.cu", "dgemm.cu", "dgemm_tc.cu", "crossprod.cu", "crossprod_tc.cu", "solver.cu", "bedfile.cu", "dense_solve.cu", "sparse_plink.cu"]
+SOURCES = ["abi.cu", "repack.cu", "dgemm.cu", "dgemm_tc.cu", "crossprod.cu", "crossprod_tc.cu",
+           "crossprod_host.cu", "multi.cu", "stager.cu", "solver.cu", "bedfile.cu", "dense_solve.cu",
+           "sparse_plink.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+         "-Xcompiler", "-fPIC,-pthread", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 
 
 def _deps_mtime() -> float:
@@ -48,7 +50,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcusolver"]
+    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcusolver", "-lpthread", "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)

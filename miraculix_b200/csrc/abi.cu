@@ -8,10 +8,47 @@
 #include <string.h>
 #include <new>
 #include "../../include/miraculix_b200.h"
+#include <nvtx3/nvToolsExt.h>
+#include <mutex>
 #include "common.cuh"
 #include "handle.h"
+#include "multi.h"
 
 namespace mb200 {
+
+NvtxRange::NvtxRange(const char *name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
+
+// One library-owned memory pool per device for stream-ordered scratch (crossproduct slabs, tile
+// lists): keeps up to 4 GB cached between calls -- a GBLUP script calls the crossproduct
+// repeatedly and the operand slab otherwise costs ~10 ms of allocation per call -- without touching
+// the process-wide default pool's settings.
+cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t stream) {
+  static std::mutex mu;
+  static cudaMemPool_t pools[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaMallocAsync(p, bytes, stream);
+  cudaMemPool_t pool;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!pools[dev]) {
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      e = cudaMemPoolCreate(&pools[dev], &props);
+      if (e != cudaSuccess) { pools[dev] = nullptr; return e; }
+      uint64_t keep = 4ull << 30;
+      if (const char *env = getenv("MB200_POOL_KEEP_GB")) keep = (uint64_t)(atof(env) * 1073741824.0);
+      cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    pool = pools[dev];
+  }
+  return cudaMallocFromPoolAsync(p, bytes, pool, stream);
+}
 
 std::atomic<unsigned long long> g_kernel_launches{0};
 
@@ -33,25 +70,46 @@ int fail(int code, const char *func, int line, const char *fmt, ...) {
 }
 
 int print_level() {
-  static int lvl = -100;
-  if (lvl == -100) {
+  static const int lvl = [] {
     const char *e = getenv("PRINT_LEVEL");
-    lvl = e ? atoi(e) : -1;  // quiet by default
-  }
+    return e ? atoi(e) : -1;  // quiet by default
+  }();
   return lvl;
 }
 
+// PRINT_LEVEL (reference cuda_utils.cu:44-82): >= 0 prints a one-time banner and a summary line per
+// entry point, > 0 adds per-call details (the reference's cyan debug_info lines).  Unset = quiet:
+// stdout belongs to the host program (the reference defaults to level 0).
+void print_banner_once() {
+  static std::once_flag once;
+  if (print_level() < 0) return;
+  std::call_once(once, [] {
+    printf("------------------------------------------------------------\n");
+    printf("\tmiraculix_b200 - B200-native compressed-genotype library\n");
+    printf("Compiled on %s %s for sm_100a\n", __DATE__, __TIME__);
+    printf("------------------------------------------------------------\n");
+  });
+}
+void debug_info(const char *fmt, ...) {  // cuda_utils.cu:55-63
+  if (print_level() <= 0) return;
+  va_list ap;
+  va_start(ap, fmt);
+  printf("\033[36m\t ");
+  vprintf(fmt, ap);
+  printf(" \033[37m\n");
+  va_end(ap);
+}
+
 Options &options() {
-  static Options o;
-  static bool init = false;
-  if (!init) {
-    init = true;
-    if (const char *e = getenv("MB200_DGEMM_MODE")) o.dgemm_mode = atoi(e);
-    if (const char *e = getenv("MB200_DGEMM_SLICES")) o.dgemm_slices = atoi(e);
-    if (const char *e = getenv("MB200_CROSSPROD_MODE")) o.crossprod_mode = atoi(e);
-    if (const char *e = getenv("MB200_PIPE_CHUNKS")) o.pipe_chunks = atoi(e);
-    if (const char *e = getenv("MB200_PIPE_MIN_BYTES")) o.pipe_min_bytes = atof(e);
-  }
+  static Options o = [] {  // thread-safe one-time init
+    Options v;
+    if (const char *e = getenv("MB200_DGEMM_MODE")) v.dgemm_mode = atoi(e);
+    if (const char *e = getenv("MB200_DGEMM_SLICES")) v.dgemm_slices = atoi(e);
+    if (const char *e = getenv("MB200_CROSSPROD_MODE")) v.crossprod_mode = atoi(e);
+    if (const char *e = getenv("MB200_PIPE_CHUNKS")) v.pipe_chunks = atoi(e);
+    if (const char *e = getenv("MB200_PIPE_MIN_BYTES")) v.pipe_min_bytes = atof(e);
+    return v;
+  }();
   return o;
 }
 
@@ -93,14 +151,29 @@ int select_device() {
     return -1;
   }
   cudaDeviceProp p;
-  if (cudaGetDeviceProperties(&p, dev) == cudaSuccess && p.major != 10)
-    fprintf(stderr, "miraculix_b200: warning: device %d is sm_%d%d; kernels are built for sm_100a\n",
-            dev, p.major, p.minor);
+  if (cudaGetDeviceProperties(&p, dev) == cudaSuccess) {
+    if (p.major != 10)
+      fprintf(stderr, "miraculix_b200: warning: device %d is sm_%d%d; kernels are built for sm_100a\n",
+              dev, p.major, p.minor);
+    if (print_level() >= 0) {  // cuda_utils.cu:204-217
+      print_banner_once();
+      const char *env = getenv("CUDA_DEVICE");
+      if (env) printf("Environment variable CUDA_DEVICE is set to %s. ", env);
+      else printf("Environment variable CUDA_DEVICE is not set. ");
+      printf("Using device %s (device no %d).\n", p.name, dev);
+    }
+  }
   return dev;
 }
 
 Handle *as_handle(void *p) {
   Handle *h = reinterpret_cast<Handle *>(p);
+  if (h && h->magic == kMultiMagic) {
+    fail(-31, __func__, __LINE__,
+         "this entry point needs a single-device handle (the handle is sharded over several devices: "
+         "use the host-pointer calls, or mb200_get_shard for a shard's handle)");
+    return nullptr;
+  }
   if (!h || h->magic != kHandleMagic) {
     fail(-5, __func__, __LINE__, "invalid compressed handle %p", p);
     return nullptr;
@@ -130,7 +203,7 @@ void destroy_handle(Handle *h) {
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int i = 0; i < Handle::kPipeMax; i++)
     if (h->ev_pipe[i]) cudaEventDestroy(h->ev_pipe[i]);
-  if (h->pinned) cudaFreeHost(h->pinned);
+  h->stager.destroy();
   for (int i = 0; i < Handle::kEvRing; i++) {
     if (h->ev_begin[i]) cudaEventDestroy(h->ev_begin[i]);
     if (h->ev_end[i]) cudaEventDestroy(h->ev_end[i]);
@@ -141,12 +214,17 @@ void destroy_handle(Handle *h) {
 }
 
 // Allocate everything a handle owns (device layout + per-call scratch); no repack yet.
-int create_handle(long snps, long indiv, int max_n, Handle **out) {
+int create_handle(long snps, long indiv, int max_n, Handle **out, int device) {
   *out = nullptr;
   if (snps <= 0 || indiv <= 0) return fail(-2, __func__, __LINE__, "snps=%ld indiv=%ld", snps, indiv);
   if (max_n < 1) max_n = 1;
-  const int dev = select_device();
-  if (dev < 0) return status().code;
+  int dev = device;
+  if (dev < 0) {
+    dev = select_device();
+    if (dev < 0) return status().code;
+  } else {
+    MB_CUDA(cudaSetDevice(dev));
+  }
   Handle *h = new (std::nothrow) Handle();
   if (!h) return fail(-6, __func__, __LINE__, "out of host memory");
   h->device = dev;
@@ -192,18 +270,19 @@ int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count);
 
 // Host bed -> device layout: stream the bed through two device staging buffers in chunks of
 // whole 512-SNP tiles and repack each chunk as it lands.
-static int repack_from_host(Handle *h, const uint8_t *plink) {
+int repack_from_host(Handle *h, const uint8_t *plink) {
   const long bs = ceil_div(h->indiv, 4);
   long rows_per_chunk = (256L << 20) / bs / 512 * 512;
   if (rows_per_chunk < 512) rows_per_chunk = 512;
   if (rows_per_chunk > round_up(h->snps, 512)) rows_per_chunk = round_up(h->snps, 512);
   uint8_t *stage[2] = {nullptr, nullptr};
-  cudaEvent_t done[2];
-  for (int i = 0; i < 2; i++) {
-    MB_CUDA(cudaMalloc(&stage[i], (size_t)rows_per_chunk * bs));
-    MB_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
-  }
+  cudaEvent_t done[2] = {nullptr, nullptr};
   int rc = 0, b = 0;
+  for (int i = 0; i < 2 && !rc; i++) {  // no early return: everything acquired here is released below
+    cudaError_t e = cudaMalloc(&stage[i], (size_t)rows_per_chunk * bs);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+    if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "staging buffers: %s", cudaGetErrorString(e));
+  }
   for (long s = 0; s < h->snps && rc == 0; s += rows_per_chunk, b ^= 1) {
     const long cnt = h->snps - s < rows_per_chunk ? h->snps - s : rows_per_chunk;
     cudaEventSynchronize(done[b]);  // staging buffer free again
@@ -215,10 +294,27 @@ static int repack_from_host(Handle *h, const uint8_t *plink) {
   }
   cudaStreamSynchronize(h->stream);
   for (int i = 0; i < 2; i++) {
-    cudaFree(stage[i]);
-    cudaEventDestroy(done[i]);
+    if (stage[i]) cudaFree(stage[i]);
+    if (done[i]) cudaEventDestroy(done[i]);
   }
   return rc;
+}
+
+// Allele frequencies (the caller's, or counts / (2 indiv) from the repack when f_host == nullptr:
+// missing genotypes count as 0 there, MXinfo.h:143), their host copy, and the row-sum maxima of
+// both orientations.  Synchronises the handle's stream.
+int finish_handle(Handle *h, const double *f_host) {
+  h->h_f.resize(h->snps);
+  if (f_host) {
+    memcpy(h->h_f.data(), f_host, sizeof(double) * h->snps);
+    MB_CUDA(cudaMemcpyAsync(h->d_f, f_host, sizeof(double) * h->snps, cudaMemcpyHostToDevice, h->stream));
+  } else {
+    MB_CHECK(freq_from_counts(h));
+    MB_CUDA(cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * h->snps, cudaMemcpyDeviceToHost,
+                            h->stream));
+  }
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  return rowsum_maxima(h);
 }
 
 }  // namespace mb200
@@ -286,23 +382,20 @@ int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long 
   Handle *h = nullptr;
   MB_CHECK(create_handle(snps, indiv, max_n, &h));
   int rc = repack_from_device(h, d_plink);
-  if (!rc) {
-    if (d_f) {
-      cudaError_t e = cudaMemcpyAsync(h->d_f, d_f, sizeof(double) * snps, cudaMemcpyDeviceToDevice,
-                                      h->stream);
-      if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
-    } else {
-      rc = freq_from_counts(h);
+  if (!rc && d_f) {
+    cudaError_t e = cudaMemcpyAsync(h->d_f, d_f, sizeof(double) * snps, cudaMemcpyDeviceToDevice, h->stream);
+    if (e == cudaSuccess) {
+      h->h_f.resize(snps);
+      e = cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * snps, cudaMemcpyDeviceToHost, h->stream);
     }
-  }
-  if (!rc) {
-    h->h_f.resize(snps);
-    cudaError_t e = cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * snps,
-                                    cudaMemcpyDeviceToHost, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+    if (!rc) rc = rowsum_maxima(h);
+  } else if (!rc) {
+    // d_f == NULL: f = allele counts / (2 indiv) with missing genotypes counted as 0 (the repack's
+    // counts; read_bed's popcount rule differs on missings and is what mb200_read_bed applies)
+    rc = finish_handle(h, nullptr);
   }
-  if (!rc) rc = rowsum_maxima(h);
   if (rc) { destroy_handle(h); return rc; }
   *compressed = h;
   return 0;
@@ -310,27 +403,83 @@ int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long 
 
 void plink2compressed(char *plink, char *plink_transposed, int snps, int indiv, double *f,
                       int max_n, void **compressed) {
+  MB_RANGE();
   (void)plink_transposed;  // both orientations are produced on the GPU from `plink`
   clear_status();
   if (!compressed) { fail(-2, __func__, __LINE__, "compressed == NULL"); return; }
   *compressed = nullptr;
   if (!plink || !f) { fail(-2, __func__, __LINE__, "plink or f is NULL"); return; }
-  Handle *h = nullptr;
-  if (create_handle(snps, indiv, max_n, &h)) return;
-  int rc = repack_from_host(h, reinterpret_cast<const uint8_t *>(plink));
-  if (!rc) {
-    h->h_f.assign(f, f + snps);
-    cudaError_t e = cudaMemcpyAsync(h->d_f, f, sizeof(double) * snps, cudaMemcpyHostToDevice,
-                                    h->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+  std::vector<int> devs;
+  if (multi_device_list(&devs)) return;
+  if (devs.size() > 1) {  // MIRACULIX_NGPUS / CUDA_DEVICE list: SNP blocks sharded over the devices
+    multi_create(devs, snps, indiv, max_n, MultiSource::HostBed, reinterpret_cast<const uint8_t *>(plink), f,
+                 0, compressed);
+    return;
   }
-  if (!rc) rc = rowsum_maxima(h);
+  Handle *h = nullptr;
+  if (create_handle(snps, indiv, max_n, &h, devs.empty() ? -1 : devs[0])) return;
+  int rc = repack_from_host(h, reinterpret_cast<const uint8_t *>(plink));
+  if (!rc) rc = finish_handle(h, f);
   if (rc) { destroy_handle(h); return; }
-  if (print_level() > 0)
+  if (print_level() >= 0)
     printf("miraculix_b200: %d SNPs x %d individuals resident on device %d (%.1f MB)\n", snps,
            indiv, h->device, ((double)snps * h->pitch_s + (double)indiv * h->pitch_i) / 1e6);
   *compressed = h;
+}
+
+// Handle from the on-device simulator (benchmarks, tests: inputs of configs[2..4] size never cross
+// PCIe); one device or sharded like plink2compressed.  The matrix depends on (seed, snps, indiv)
+// only, not on the number of devices.
+int mb200_simulate_compressed(long snps, long indiv, unsigned long long seed, int max_n,
+                              void **compressed) {
+  MB_RANGE();
+  clear_status();
+  if (!compressed) return fail(-2, __func__, __LINE__, "compressed == NULL");
+  *compressed = nullptr;
+  std::vector<int> devs;
+  MB_CHECK(multi_device_list(&devs));
+  if (devs.size() > 1)
+    return multi_create(devs, snps, indiv, max_n, MultiSource::Simulated, nullptr, nullptr, seed, compressed);
+  Handle *h = nullptr;
+  MB_CHECK(create_handle(snps, indiv, max_n, &h, devs.empty() ? -1 : devs[0]));
+  uint8_t *d_bed = nullptr;
+  cudaError_t e = cudaMalloc(&d_bed, (size_t)snps * ceil_div(indiv, 4));
+  int rc = e == cudaSuccess ? 0 : fail((int)e, __func__, __LINE__, "bed buffer: %s", cudaGetErrorString(e));
+  if (!rc) rc = simulate_plink(d_bed, snps, indiv, seed, h->stream, 0);
+  if (!rc) rc = repack_from_device(h, d_bed);
+  if (!rc) rc = finish_handle(h, nullptr);
+  cudaFree(d_bed);
+  if (rc) { destroy_handle(h); return rc; }
+  *compressed = h;
+  return 0;
+}
+
+int mb200_set_devices(int n, const int *devices) {
+  clear_status();
+  return multi_set_devices(n, devices);
+}
+int mb200_shard_count(void *compressed) {
+  clear_status();
+  if (MultiHandle *m = as_multi(compressed)) return multi_shards(m);
+  return as_handle(compressed) ? 1 : -1;
+}
+int mb200_get_shard(void *compressed, int g, void **shard, long *snp_begin, long *snp_count) {
+  clear_status();
+  if (!shard) return fail(-2, __func__, __LINE__, "shard == NULL");
+  *shard = nullptr;
+  if (MultiHandle *m = as_multi(compressed)) {
+    Handle *h = multi_shard(m, g, snp_begin, snp_count);
+    if (!h) return fail(-2, __func__, __LINE__, "shard %d of %d", g, multi_shards(m));
+    *shard = h;
+    return 0;
+  }
+  Handle *h = as_handle(compressed);
+  if (!h) return status().code;
+  if (g != 0) return fail(-2, __func__, __LINE__, "shard %d of 1", g);
+  if (snp_begin) *snp_begin = 0;
+  if (snp_count) *snp_count = h->snps;
+  *shard = h;
+  return 0;
 }
 
 int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
@@ -382,6 +531,7 @@ int mb200_dgemm_last_precision(void *compressed, int *slices) {
   return dgemm_tc_last_precision(h, slices);
 }
 int mb200_sync(void *compressed) {
+  if (MultiHandle *m = as_multi(compressed)) return multi_sync(m);
   Handle *h = as_handle(compressed);
   if (!h) return status().code;
   MB_CUDA(cudaStreamSynchronize(h->stream));
@@ -404,17 +554,12 @@ static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, do
   if (n <= 0) return 0;
   if (options().dgemm_mode == 1)  // tensor-core path: PCIe copies pipelined against the kernels
     return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc, 0, 0);
-  if (ldb == k)
-    MB_CUDA(cudaMemcpyAsync(h->d_B, B, sizeof(double) * k * n, cudaMemcpyHostToDevice, h->stream));
-  else
-    MB_CUDA(cudaMemcpy2DAsync(h->d_B, sizeof(double) * k, B, sizeof(double) * ldb,
-                              sizeof(double) * k, n, cudaMemcpyHostToDevice, h->stream));
+  const bool b_pin = host_is_pinned(B), c_pin = host_is_pinned(C);
+  if (!b_pin || !c_pin) MB_CHECK(h->stager.init(4u << 20));
+  MB_CHECK(panel_h2d(&h->stager, b_pin, h->d_B, k, B, ldb, k, n, h->stream));
   MB_CHECK(dgemm_device(h, trans, n, h->d_B, k, h->d_C, m));
-  if (ldc == m)
-    MB_CUDA(cudaMemcpyAsync(C, h->d_C, sizeof(double) * m * n, cudaMemcpyDeviceToHost, h->stream));
-  else
-    MB_CUDA(cudaMemcpy2DAsync(C, sizeof(double) * ldc, h->d_C, sizeof(double) * m,
-                              sizeof(double) * m, n, cudaMemcpyDeviceToHost, h->stream));
+  MB_CHECK(panel_d2h(&h->stager, c_pin, C, ldc, h->d_C, m, m, n, h->stream));
+  if (!c_pin) MB_CHECK(h->stager.drain());
   MB_CUDA(cudaStreamSynchronize(h->stream));
   return 0;
 }
@@ -438,32 +583,46 @@ int mb200_dgemm_compressed_mixed(int trans, void *compressed, int n, const doubl
   // fp64 SIMT family: plain staging
   const double *dB = B;
   double *dC = C;
+  const bool b_pin = b_on_device || host_is_pinned(B), c_pin = c_on_device || host_is_pinned(C);
+  if (!b_pin || !c_pin) MB_CHECK(h->stager.init(4u << 20));
   if (!b_on_device) {
-    MB_CUDA(cudaMemcpy2DAsync(h->d_B, sizeof(double) * k, B, sizeof(double) * ldb, sizeof(double) * k,
-                              n, cudaMemcpyHostToDevice, h->stream));
+    MB_CHECK(panel_h2d(&h->stager, b_pin, h->d_B, k, B, ldb, k, n, h->stream));
     dB = h->d_B;
     ldb = k;
   }
   if (!c_on_device) dC = h->d_C;
   MB_CHECK(dgemm_device(h, trans, n, dB, ldb, dC, c_on_device ? ldc : m));
-  if (!c_on_device)
-    MB_CUDA(cudaMemcpy2DAsync(C, sizeof(double) * ldc, h->d_C, sizeof(double) * m, sizeof(double) * m,
-                              n, cudaMemcpyDeviceToHost, h->stream));
+  if (!c_on_device) {
+    MB_CHECK(panel_d2h(&h->stager, c_pin, C, ldc, h->d_C, m, m, n, h->stream));
+    if (!c_pin) MB_CHECK(h->stager.drain());
+  }
   MB_CUDA(cudaStreamSynchronize(h->stream));
   return 0;
 }
 
 void dgemm_compressed(char *trans, void *compressed, int n, double *B, int Ldb, double *C, int Ldc) {
+  MB_RANGE();
   clear_status();
   const int t = is_trans(trans);
+  if (MultiHandle *m = as_multi(compressed)) {
+    multi_dgemm_host(m, t, n, B, Ldb, C, Ldc);
+    return;
+  }
   Handle *h = as_handle(compressed);
   if (!h) return;
   dgemm_host(h, t, n, B, Ldb, C, Ldc);
+  debug_info("dgemm_compressed '%c' n=%d on device %d: %d digits", t ? 'T' : 'N', n, h->device, h->last_slices);
 }
 
 void free_compressed(void **compressed) {
+  MB_RANGE();
   clear_status();
   if (!compressed || !*compressed) return;
+  if (MultiHandle *m = as_multi(*compressed)) {
+    multi_destroy(m);
+    *compressed = nullptr;
+    return;
+  }
   Handle *h = reinterpret_cast<Handle *>(*compressed);
   if (h->magic != kHandleMagic) { fail(-5, __func__, __LINE__, "invalid handle"); return; }
   destroy_handle(h);
@@ -472,6 +631,10 @@ void free_compressed(void **compressed) {
 
 void get_compressed_freq(void *compressed, double *f) {
   clear_status();
+  if (MultiHandle *m = as_multi(compressed)) {
+    if (f) multi_get_freq(m, f);
+    return;
+  }
   Handle *h = as_handle(compressed);
   if (!h || !f) return;
   memcpy(f, h->h_f.data(), sizeof(double) * h->snps);
@@ -573,47 +736,54 @@ int mb200_crossprod_last_timing(double out[3]) {
   return 0;
 }
 
-// host-pointer crossproduct: H2D packed matrix, device pipeline, D2H fp64 result
+// Host-pointer crossproduct.  Counts and GRM: the tiled out-of-core path over the selected devices
+// (crossprod_host.cu; device memory bounded by TILE_SIZE / MB200_GRM_ACC_GB, not by rows^2).  LD
+// needs the finished diagonal before it can scale, so it stays in core on one device.
 static int crossprod_host(const unsigned char *x, int k, int rows, double *ans, int is_plink,
                           int mode, const double *f, int do_scale) {
+  MB_RANGE();
   clear_status();
   if (!x || !ans || k <= 0 || rows <= 0)
     return fail(-2, __func__, __LINE__, "bad arguments (k=%d rows=%d)", k, rows) ? 1 : 1;
-  if (select_device() < 0) return 1;
+  std::vector<int> devs;
+  if (multi_device_list(&devs)) return 1;
+  if (mode != 2) {
+    const int rc = crossprod_host_tiled(x, k, rows, ans, is_plink, mode, f, do_scale, devs, &t_cp_timing);
+    if (!rc && print_level() >= 0)
+      printf("miraculix_b200: crossproduct %d x %d on %d device(s): device pipeline %.2f ms\n", rows, k,
+             devs.empty() ? 1 : (int)devs.size(), t_cp_timing.gemm_ms);
+    return rc ? 1 : 0;
+  }
+  if (devs.size() >= 1) {
+    if (cudaSetDevice(devs[0]) != cudaSuccess) return fail(-4, __func__, __LINE__, "cudaSetDevice(%d) failed", devs[0]) ? 1 : 1;
+  } else if (select_device() < 0) {
+    return 1;
+  }
   const long nb = ceil_div(k, 4);
   uint8_t *d_x = nullptr;
   double *d_ans = nullptr, *d_f = nullptr;
+  cudaStream_t st = nullptr;
   int rc = 0;
   cudaError_t e;
 #define X_CUDA(expr)                                                                     \
   if (!rc && (e = (expr)) != cudaSuccess)                                                 \
     rc = fail((int)e, __func__, __LINE__, "%s: %s", #expr, cudaGetErrorString(e))
-  // Stream-ordered allocations from the device's default pool, which keeps up to 4 GB cached
-  // between calls: a GBLUP script calls this entry repeatedly and the 800 MB result buffer plus the
-  // int8 operand slab of crossprod_device otherwise cost ~10 ms of cudaMalloc/cudaFree per call.
-  {
-    int dev = 0;
-    cudaMemPool_t pool;
-    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-      uint64_t keep = 4ull << 30;
-      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-    }
+  X_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  X_CUDA(pool_alloc(&d_x, (size_t)rows * nb, st));
+  X_CUDA(pool_alloc(&d_ans, sizeof(double) * rows * rows, st));
+  X_CUDA(cudaMemcpyAsync(d_x, x, (size_t)rows * nb, cudaMemcpyHostToDevice, st));
+  if (f) {
+    X_CUDA(pool_alloc(&d_f, sizeof(double) * rows, st));
+    X_CUDA(cudaMemcpyAsync(d_f, f, sizeof(double) * rows, cudaMemcpyHostToDevice, st));
   }
-  X_CUDA(cudaMallocAsync(&d_x, (size_t)rows * nb, 0));
-  X_CUDA(cudaMallocAsync(&d_ans, sizeof(double) * rows * rows, 0));
-  X_CUDA(cudaMemcpyAsync(d_x, x, (size_t)rows * nb, cudaMemcpyHostToDevice, 0));
-  if (f && mode) {
-    const long nf = mode == 1 ? k : rows;
-    X_CUDA(cudaMallocAsync(&d_f, sizeof(double) * nf, 0));
-    X_CUDA(cudaMemcpyAsync(d_f, f, sizeof(double) * nf, cudaMemcpyHostToDevice, 0));
-  }
-  if (!rc) rc = crossprod_device(d_x, k, rows, is_plink, mode, d_f, do_scale, d_ans, 0, &t_cp_timing);
-  X_CUDA(cudaMemcpyAsync(ans, d_ans, sizeof(double) * rows * rows, cudaMemcpyDeviceToHost, 0));
-  X_CUDA(cudaStreamSynchronize(0));
+  if (!rc) rc = crossprod_device(d_x, k, rows, is_plink, mode, d_f, do_scale, d_ans, st, &t_cp_timing);
+  X_CUDA(cudaMemcpyAsync(ans, d_ans, sizeof(double) * rows * rows, cudaMemcpyDeviceToHost, st));
+  X_CUDA(cudaStreamSynchronize(st));
 #undef X_CUDA
-  if (d_x) cudaFreeAsync(d_x, 0);
-  if (d_ans) cudaFreeAsync(d_ans, 0);
-  if (d_f) cudaFreeAsync(d_f, 0);
+  if (d_x) cudaFreeAsync(d_x, st);
+  if (d_ans) cudaFreeAsync(d_ans, st);
+  if (d_f) cudaFreeAsync(d_f, st);
+  if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
   return rc ? 1 : 0;
 }
 

@@ -19,8 +19,6 @@
 namespace mb200 {
 
 int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count);
-int create_handle(long snps, long indiv, int max_n, Handle **out);
-void destroy_handle(Handle *h);
 
 // f[s] = popcount(row s) / (2 indiv): one warp per SNP row of the staged chunk
 __global__ void __launch_bounds__(256)

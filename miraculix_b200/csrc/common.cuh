@@ -20,6 +20,8 @@ Status &status();
 int fail(int code, const char *func, int line, const char *fmt, ...);
 void clear_status();
 int print_level();  // PRINT_LEVEL env, src/cuda/cuda_utils.cu:44-63
+void print_banner_once();                 // cuda_utils.cu:65-82, at PRINT_LEVEL >= 0
+void debug_info(const char *fmt, ...);    // cuda_utils.cu:55-63, at PRINT_LEVEL > 0
 
 extern std::atomic<unsigned long long> g_kernel_launches;
 inline void count_launch(unsigned n = 1) { g_kernel_launches.fetch_add(n, std::memory_order_relaxed); }
@@ -44,6 +46,23 @@ static inline long ceil_div(long x, long m) { return (x + m - 1) / m; }
 
 int device_sm_count(int device);
 int select_device();  // CUDA_DEVICE env (src/cuda/cuda_utils.cu:188-248), default 0
+// Stream-ordered scratch comes from a memory pool the LIBRARY owns (one per device, keeps up to
+// 4 GB cached between calls): the process-wide default pool is left as the host program set it.
+cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t stream);
+template <typename T> inline cudaError_t pool_alloc(T **p, size_t bytes, cudaStream_t stream) {
+  void *q = nullptr;
+  const cudaError_t e = pool_alloc(&q, bytes, stream);
+  *p = static_cast<T *>(q);
+  return e;
+}
+
+// NVTX range around an ABI entry point (nvtx3 is header-only; a no-op without a profiler attached).
+// The reference brackets the same calls with wall-clock prints (snp_multiply_cuda.cu:45-46, 354-366).
+struct NvtxRange {
+  explicit NvtxRange(const char *name);
+  ~NvtxRange();
+};
+#define MB_RANGE() ::mb200::NvtxRange _mb_range(__func__)
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------------------

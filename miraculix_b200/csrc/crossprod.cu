@@ -34,7 +34,7 @@ struct CallScratch {
   explicit CallScratch(cudaStream_t s) : stream(s) {}
   template <typename T> cudaError_t alloc(T **p, size_t bytes) {
     void *q = nullptr;
-    const cudaError_t e = n < 8 ? cudaMallocAsync(&q, bytes, stream) : cudaErrorMemoryAllocation;
+    const cudaError_t e = n < 8 ? pool_alloc(&q, bytes, stream) : cudaErrorMemoryAllocation;
     if (e == cudaSuccess) ptrs[n++] = q;
     *p = static_cast<T *>(q);
     return e;
@@ -352,6 +352,70 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
     timing->executed_ops = executed_ops;
   }
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Building blocks of the out-of-core / multi-device host path (crossprod_host.cu): the int32
+// counts of one partition's row tiles over all K slabs (no fp64 epilogue: the finishing kernel
+// there converts chunk by chunk while earlier chunks are on their way to the host), and the GRM
+// row sums.  C32: [round_up(local_rows, 256)][round_up(rows, 256)] int32; the entries of local
+// row lr (global row i) are valid from column 256 floor(i / 256) on.
+// ---------------------------------------------------------------------------------------------
+int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int part,
+                               int nparts, int32_t *C32, cudaStream_t stream, double *executed_ops) {
+  if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
+  if (nparts < 1 || part < 0 || part >= nparts)
+    return fail(-2, __func__, __LINE__, "bad partition %d of %d", part, nparts);
+  int device = 0;
+  MB_CUDA(cudaGetDevice(&device));
+  const int sms = device_sm_count(device);
+  const long nb = ceil_div(k, 4);
+  const long rows_pad = round_up(rows, 256);
+  if (crossprod_partition_rows(rows, part, nparts) == 0) return 0;
+  double slab_gb = 8.0;
+  if (const char *e = getenv("MB200_SLAB_GB")) slab_gb = atof(e) > 0 ? atof(e) : slab_gb;
+  long slab_kbytes = (long)(slab_gb * 1073741824.0 / (double)rows_pad) / 4 / 32 * 32;
+  if (slab_kbytes < 32) slab_kbytes = 32;
+  if (slab_kbytes > round_up(nb, 32)) slab_kbytes = round_up(nb, 32);
+  const long kpad = slab_kbytes * 4;
+  if (is_plink_format) MB_CHECK(upload_lut());
+  int8_t *X8 = nullptr;
+  TileCoord *d_tiles = nullptr;
+  int num_tiles = 0, real_tiles = 0, num_tail = 0;
+  CallScratch scratch(stream);
+  MB_CUDA(scratch.alloc(&X8, (size_t)rows_pad * kpad));
+  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? nparts : 0;
+  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, 0,
+                           crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
+  scratch.adopt(d_tiles);
+  int slab = 0;
+  for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
+    const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
+    const long kuse = round_up(kbytes * 4, 128);
+    expand_2bit_launch(d_x, rows, nb, kb0, kbytes, is_plink_format, X8, rows_pad, kpad, sms, stream);
+    count_launch();
+    MB_LAUNCH_CHECK();
+    MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
+                                 sms, stream, nullptr, 0, pair));
+    if (executed_ops) *executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
+  }
+  return 0;  // `scratch` frees stream-ordered: the slab outlives the kernels enqueued above
+}
+
+// d_m[0..rows) = M 1, d_m[rows] = sum of them, d_m[rows + 1] = 2 sum f (1 - f) (do_scale); d_m holds
+// rows + 8 doubles.  In line on `stream`.
+int crossprod_row_sums(const uint8_t *d_x, long k, long rows, int is_plink_format, const double *d_f,
+                       int do_scale, double *d_m, cudaStream_t stream) {
+  if (do_scale && !d_f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+  const long nb = ceil_div(k, 4);
+  if (is_plink_format) MB_CHECK(upload_lut());
+  int device = 0;
+  MB_CUDA(cudaGetDevice(&device));
+  unsigned int *d_s = nullptr;
+  CallScratch scratch(stream);
+  MB_CUDA(scratch.alloc(&d_s, sizeof(unsigned int) * input_row_sums_scratch(nb)));
+  cudaEvent_t join = nullptr;
+  return grm_row_sums(d_x, rows, nb, k, is_plink_format, d_f, do_scale, d_s, d_m, device, stream, false, &join);
 }
 
 }  // namespace mb200

@@ -1,0 +1,279 @@
+// crossprod_host.cu -- host-pointer crossproduct / GRM, out of core and over several devices.
+//
+// Replaces the host tile loop of the reference (src/cuda/snp_multiply_cuda.cu:190-340: per tile
+// pair H2D, CUTLASS launch, D2H of an int32 tile, host cast + scatter into ans[i,j] and ans[j,i])
+// and keeps its property that device memory does not grow with indiv^2 (TILE_SIZE, :53-74).
+//
+// Device g of N (one host thread each, team.h):
+//   1. uploads 1/N of the packed matrix and pulls the rest from the peers (NVLink), so the input
+//      crosses PCIe once in total;
+//   2. for every pass t: accumulates the int32 counts of partition g + N t of N * passes (cyclic
+//      128-row tiles: balanced over the upper triangle, crossprod.cu) over all K slabs;
+//   3. finish_chunk_kernel turns a chunk of row tiles into fp64 -- with the exact GRM update of
+//      crossproduct.jl:91-106 -- in BOTH orientations, and the chunk streams into the caller's
+//      column-major matrix as it is: rows of the panel are columns of `ans` below the diagonal,
+//      the transposed copy fills the part above it (the reference's ans[j,i] = ans[i,j] scatter).
+//      Chunks are double-buffered: the copy of one overlaps the finishing of the next and the
+//      GEMM of the next pass.
+// Pageable `ans` / `x` (Julia, Fortran arrays) go through the pinned ring of stager.h.
+#include <stdlib.h>
+#include <string.h>
+#include <memory>
+#include "common.cuh"
+#include "multi.h"
+#include "team.h"
+
+namespace mb200 {
+
+constexpr int FC_T = 32;  // 32 x 32 sub-tiles
+
+// counts C32[lr][j] (ld32) of local rows [lr0, lr0 + crows) -> P[lr - lr0][j] (row-major, ld n) and
+// PT[j][lr - lr0] (ld crows).  Global row of local row lr: ((lr / 128) nparts + part) 128 + lr % 128.
+// Only columns from the row tile's first computed column tile on are produced.
+__global__ void __launch_bounds__(256)
+finish_chunk_kernel(const int32_t *__restrict__ C32, long ld32, long lr0, long crows, long n,
+                    int part, int nparts, int affine, int do_scale, const double *__restrict__ m,
+                    const double *__restrict__ scal, double *__restrict__ P, double *__restrict__ PT) {
+  __shared__ double t[FC_T][FC_T + 1];
+  const long rb = (long)blockIdx.y * FC_T;          // row offset inside the chunk
+  const long lt = (lr0 + rb) / 128;                 // local row tile
+  const long gi0 = (lt * nparts + part) * 128 + (lr0 + rb) % 128;  // global row of sub-tile row 0
+  const long first = ((lt * nparts + part) & ~1L) * 128;
+  const long j0 = (long)blockIdx.x * FC_T;
+  if (j0 + FC_T <= first || gi0 >= n) return;       // left of the diagonal tile / row padding
+  const CpAffine aff = cp_affine_setup(n, affine, do_scale, scal);
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int yy = ty; yy < FC_T; yy += 8) {
+    const long gi = gi0 + yy, j = j0 + tx;
+    double v = 0.0;
+    if (gi < n && j < n && j >= first) {
+      const int cnt = C32[(lr0 + rb + yy) * ld32 + j];
+      v = affine ? cp_affine_m(cnt, m[gi], m[j], aff) : (double)cnt;
+      P[(rb + yy) * n + j] = v;
+    }
+    t[yy][tx] = v;
+  }
+  __syncthreads();
+  for (int yy = ty; yy < FC_T; yy += 8) {
+    const long j = j0 + yy, gi = gi0 + tx;
+    if (gi < n && j < n && j >= first) PT[j * crows + rb + tx] = t[tx][yy];
+  }
+}
+
+namespace {
+
+struct DevCtx {
+  int device = 0;
+  cudaStream_t s_main = nullptr, s_copy = nullptr;
+  uint8_t *d_x = nullptr;
+  double *d_f = nullptr, *d_m = nullptr;
+  int32_t *C32 = nullptr;
+  double *P[2] = {nullptr, nullptr}, *PT[2] = {nullptr, nullptr};
+  cudaEvent_t fin[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr}, up = nullptr;
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  Stager stager;
+  double ops = 0.0;
+  void release() {
+    if (s_main) cudaStreamSynchronize(s_main);
+    if (s_copy) cudaStreamSynchronize(s_copy);
+    cudaFree(d_x);
+    cudaFree(d_f);
+    cudaFree(d_m);
+    cudaFree(C32);
+    for (int b = 0; b < 2; b++) {
+      cudaFree(P[b]);
+      cudaFree(PT[b]);
+      if (fin[b]) cudaEventDestroy(fin[b]);
+      if (freed[b]) cudaEventDestroy(freed[b]);
+    }
+    if (up) cudaEventDestroy(up);
+    if (t0) cudaEventDestroy(t0);
+    if (t1) cudaEventDestroy(t1);
+    stager.destroy();
+    if (s_main) cudaStreamDestroy(s_main);
+    if (s_copy) cudaStreamDestroy(s_copy);
+  }
+};
+
+// flat byte upload, through the stager's ring when the source is pageable
+int upload_bytes(DevCtx &c, bool pinned, uint8_t *d, const uint8_t *h, size_t bytes) {
+  if (!bytes) return 0;
+  if (pinned) {
+    MB_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c.s_main));
+    return 0;
+  }
+  const size_t whole = bytes / 8;  // the ring moves doubles; the (< 8 byte) tail goes directly
+  if (whole) MB_CHECK(c.stager.upload(reinterpret_cast<double *>(d), (long)whole,
+                                      reinterpret_cast<const double *>(h), (long)whole, (long)whole, 1, c.s_main));
+  if (bytes % 8) MB_CUDA(cudaMemcpyAsync(d + whole * 8, h + whole * 8, bytes % 8, cudaMemcpyHostToDevice, c.s_main));
+  return 0;
+}
+
+}  // namespace
+
+int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int is_plink, int mode,
+                         const double *f, int do_scale, const std::vector<int> &devs_in,
+                         CrossprodTiming *timing) {
+  if (!x || !ans || k <= 0 || rows <= 0) return fail(-2, __func__, __LINE__, "bad arguments (k=%ld rows=%ld)", k, rows);
+  if (mode < 0 || mode > 1) return fail(-2, __func__, __LINE__, "mode %d not supported on the tiled path", mode);
+  if (mode == 1 && (double)rows * (double)rows * 4.0 * (double)k >= 4.0e18)
+    return fail(-2, __func__, __LINE__, "GRM of %ld x %ld exceeds the exact integer epilogue", rows, k);
+  if (mode == 1 && do_scale && !f) return fail(-3, __func__, __LINE__, "allele frequencies required for scaling");
+  std::vector<int> devs = devs_in;
+  if (devs.empty()) {
+    const int d = select_device();
+    if (d < 0) return status().code;
+    devs.push_back(d);
+  }
+  const long Mt = ceil_div(rows, 128);
+  if ((long)devs.size() > Mt) devs.resize((size_t)Mt);
+  const int N = (int)devs.size();
+  const long nb = ceil_div(k, 4), rows_pad = round_up(rows, 256);
+
+  // Passes: the int32 accumulator of one pass holds ceil(Mt / (N passes)) row tiles.  TILE_SIZE
+  // (the reference's knob, rows here) and MB200_GRM_ACC_GB (default 16 GiB) bound it; a few passes
+  // are used even when one would fit, so that the download of one overlaps the GEMM of the next.
+  long tile_rows = 1L << 40;
+  if (const char *e = getenv("TILE_SIZE")) {
+    const long v = atol(e);
+    if (v > 0) tile_rows = v < 128 ? 128 : v / 128 * 128;
+  }
+  double acc_gb = 16.0;
+  if (const char *e = getenv("MB200_GRM_ACC_GB")) acc_gb = atof(e) > 0 ? atof(e) : acc_gb;
+  const long mem_rows = (long)(acc_gb * 1073741824.0 / 4.0 / (double)rows_pad) / 256 * 256;
+  if (mem_rows < tile_rows) tile_rows = mem_rows < 256 ? 256 : mem_rows;
+  const long tiles_per_dev = ceil_div(Mt, N);
+  long passes = ceil_div(tiles_per_dev * 128, tile_rows);
+  if (const char *e = getenv("MB200_GRM_PASSES")) passes = atol(e) > passes ? atol(e) : passes;
+  else if (passes < 3) passes = 3;
+  while (passes > 1 && N * passes * 4 > Mt && ceil_div(tiles_per_dev * 128, tile_rows) < passes) passes--;
+  if (N * passes > Mt) passes = ceil_div(Mt, N);
+  const int nparts = (int)(N * passes);
+  long acc_rows = 0;  // rows of the largest partition, padded to whole CTA pairs
+  for (int p = 0; p < nparts; p++) {
+    const long lr = round_up(crossprod_partition_rows(rows, p, nparts), 256);
+    acc_rows = lr > acc_rows ? lr : acc_rows;
+  }
+  // chunk of row tiles that is finished and downloaded at once: two orientations, two buffers
+  double chunk_mb = 128.0;
+  if (const char *e = getenv("MB200_GRM_CHUNK_MB")) chunk_mb = atof(e) > 0 ? atof(e) : chunk_mb;
+  long chunk_tiles = (long)(chunk_mb * 1048576.0 / (128.0 * 8.0 * (double)rows));
+  if (chunk_tiles < 1) chunk_tiles = 1;
+  if (chunk_tiles > acc_rows / 128) chunk_tiles = acc_rows / 128;
+  const long chunk_rows = chunk_tiles * 128;
+
+  const bool ans_pin = host_is_pinned(ans), x_pin = host_is_pinned(x);
+  std::vector<DevCtx> ctx(N);
+  Team team(N);
+  // slices of the packed rows each device uploads itself
+  std::vector<long> xr0(N + 1);
+  for (int g = 0; g <= N; g++) xr0[g] = rows * g / N;
+
+  const int rc = team.run([&](int g) -> int {
+    DevCtx &c = ctx[g];
+    c.device = devs[g];
+    MB_CUDA(cudaSetDevice(c.device));
+    for (int p = 0; p < N; p++) {  // peer access for the gather of the packed input
+      if (devs[p] == c.device) continue;
+      int can = 0;
+      MB_CUDA(cudaDeviceCanAccessPeer(&can, c.device, devs[p]));
+      if (can) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(devs[p], 0);
+        if (e != cudaSuccess) cudaGetLastError();  // already enabled, or copies fall back to staging
+      }
+    }
+    MB_CUDA(cudaStreamCreateWithFlags(&c.s_main, cudaStreamNonBlocking));
+    MB_CUDA(cudaStreamCreateWithFlags(&c.s_copy, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+      MB_CUDA(cudaEventCreateWithFlags(&c.fin[b], cudaEventDisableTiming));
+      MB_CUDA(cudaEventCreateWithFlags(&c.freed[b], cudaEventDisableTiming));
+    }
+    MB_CUDA(cudaEventCreateWithFlags(&c.up, cudaEventDisableTiming));
+    MB_CUDA(cudaEventCreate(&c.t0));
+    MB_CUDA(cudaEventCreate(&c.t1));
+    if (!ans_pin || !x_pin) MB_CHECK(c.stager.init(4u << 20));
+    MB_CUDA(cudaMalloc(&c.d_x, (size_t)rows * nb));
+    MB_CUDA(cudaMalloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad));
+    for (int b = 0; b < 2; b++) {
+      MB_CUDA(cudaMalloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows));
+      MB_CUDA(cudaMalloc(&c.PT[b], sizeof(double) * (size_t)chunk_rows * rows));
+    }
+    if (mode == 1) {
+      MB_CUDA(cudaMalloc(&c.d_m, sizeof(double) * (rows + 8)));
+      if (f) {
+        MB_CUDA(cudaMalloc(&c.d_f, sizeof(double) * k));
+        MB_CUDA(cudaMemcpyAsync(c.d_f, f, sizeof(double) * k, cudaMemcpyHostToDevice, c.s_main));
+      }
+    }
+    // 1. my rows of the packed matrix from the host, the rest from the peers
+    MB_CHECK(upload_bytes(c, x_pin, c.d_x + xr0[g] * nb, x + xr0[g] * nb, (size_t)(xr0[g + 1] - xr0[g]) * nb));
+    MB_CUDA(cudaEventRecord(c.up, c.s_main));
+    MB_CHECK(team.barrier());
+    for (int p = 0; p < N; p++) {
+      if (p == g || xr0[p + 1] == xr0[p]) continue;
+      MB_CUDA(cudaStreamWaitEvent(c.s_main, ctx[p].up, 0));
+      MB_CUDA(cudaMemcpyAsync(c.d_x + xr0[p] * nb, ctx[p].d_x + xr0[p] * nb, (size_t)(xr0[p + 1] - xr0[p]) * nb,
+                              cudaMemcpyDefault, c.s_main));
+    }
+    MB_CUDA(cudaEventRecord(c.t0, c.s_main));
+    if (mode == 1) MB_CHECK(crossprod_row_sums(c.d_x, k, rows, is_plink, c.d_f, do_scale, c.d_m, c.s_main));
+    // 2./3. passes
+    int buf = 0;
+    bool used[2] = {false, false};
+    for (long t = 0; t < passes; t++) {
+      const int part = (int)(g + N * t);
+      const long lrows = crossprod_partition_rows(rows, part, nparts);
+      if (lrows == 0) continue;
+      MB_CHECK(crossprod_partition_counts(c.d_x, k, rows, is_plink, part, nparts, c.C32, c.s_main, &c.ops));
+      for (long lr0 = 0; lr0 < lrows; lr0 += chunk_rows, buf ^= 1) {
+        const long crows = lrows - lr0 < chunk_rows ? lrows - lr0 : chunk_rows;
+        if (used[buf]) MB_CUDA(cudaStreamWaitEvent(c.s_main, c.freed[buf], 0));  // its last download is done
+        dim3 grid((unsigned)ceil_div(rows, FC_T), (unsigned)(crows / FC_T));
+        finish_chunk_kernel<<<grid, 256, 0, c.s_main>>>(c.C32, rows_pad, lr0, crows, rows, part, nparts,
+                                                        mode == 1, do_scale, c.d_m, c.d_m ? c.d_m + rows : nullptr,
+                                                        c.P[buf], c.PT[buf]);
+        count_launch();
+        MB_LAUNCH_CHECK();
+        MB_CUDA(cudaEventRecord(c.fin[buf], c.s_main));
+        MB_CUDA(cudaStreamWaitEvent(c.s_copy, c.fin[buf], 0));
+        for (long lt = lr0 / 128; lt < (lr0 + crows) / 128; lt++) {
+          const long mi = lt * nparts + part, i0 = mi * 128;
+          if (i0 >= rows) break;
+          const long first = (mi & ~1L) * 128, trows = rows - i0 < 128 ? rows - i0 : 128;
+          const long lo = (lt * 128 - lr0);  // row of this tile inside the chunk
+          // rows of the panel = columns of ans from `first` down
+          MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + first + i0 * rows, rows, c.P[buf] + lo * rows + first,
+                             rows, rows - first, (int)trows, c.s_copy));
+          // transposed panel = rows i of the columns right of `first`
+          MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + i0 + first * rows, rows, c.PT[buf] + lo + first * crows,
+                             crows, trows, (int)(rows - first), c.s_copy));
+        }
+        MB_CUDA(cudaEventRecord(c.freed[buf], c.s_copy));
+        used[buf] = true;
+      }
+    }
+    MB_CUDA(cudaEventRecord(c.t1, c.s_main));
+    if (!ans_pin) MB_CHECK(c.stager.drain());
+    MB_CUDA(cudaStreamSynchronize(c.s_main));
+    MB_CUDA(cudaStreamSynchronize(c.s_copy));
+    // peers may still be pulling my slice of the input
+    return team.barrier();
+  });
+  if (timing && !rc) {
+    float ms = 0;
+    cudaSetDevice(ctx[0].device);
+    cudaEventElapsedTime(&ms, ctx[0].t0, ctx[0].t1);
+    timing->gemm_ms = ms;
+    timing->epilogue_ms = 0;
+    timing->executed_ops = 0;
+    for (int g = 0; g < N; g++) timing->executed_ops += ctx[g].ops;
+  }
+  team.run([&](int g) -> int {
+    cudaSetDevice(devs[g]);
+    ctx[g].release();
+    return 0;
+  });
+  return rc;
+}
+
+}  // namespace mb200

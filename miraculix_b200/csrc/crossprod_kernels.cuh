@@ -366,6 +366,9 @@ row_dot_words_kernel(const uint32_t *__restrict__ x, long rows, long nw, int is_
 inline size_t input_row_sums_scratch(long nb) { return 2 * (size_t)(4 * nb + 16); }
 inline int input_row_sums(const uint8_t *d_x, long rows, long nb, int is_plink, unsigned int *d_s,
                           double *d_m, cudaStream_t stream) {
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  const long sms = device_sm_count(dev_);
   MB_CUDA(cudaMemsetAsync(d_s, 0, sizeof(unsigned int) * (4 * nb + 16), stream));
   int ysplit = (int)(rows / 512 < 1 ? 1 : rows / 512 > 64 ? 64 : rows / 512);
   if (nb % 4 == 0 && (reinterpret_cast<uintptr_t>(d_x) & 15) == 0) {
@@ -376,7 +379,7 @@ inline int input_row_sums(const uint8_t *d_x, long rows, long nb, int is_plink, 
     uint4 *planes = reinterpret_cast<uint4 *>(d_s + 4 * nb + 16);  // 16-byte aligned: nb % 4 == 0
     colsum_planes_kernel<<<(unsigned)ceil_div(4 * nw, 256), 256, 0, stream>>>(d_s, nw, planes);
     const long rblocks = ceil_div(rows, 8 * RD_ROWS);
-    long ks = ceil_div(148 * 6, rblocks);
+    long ks = ceil_div(sms * 6, rblocks);
     if (ks > ceil_div(nw, 256)) ks = ceil_div(nw, 256);
     if (ks < 1) ks = 1;
     MB_CUDA(cudaMemsetAsync(d_m, 0, sizeof(double) * rows, stream));

@@ -15,6 +15,7 @@
 // One CTA per SM, static round-robin over a host-built list of upper-triangle tiles that is
 // ordered in L2-friendly super-blocks.
 #include <cuda.h>
+#include <mutex>
 #include "common.cuh"
 #include "handle.h"
 
@@ -403,7 +404,7 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
   if (num_tail) *num_tail = ntail;
   if (real_tiles) *real_tiles = pair ? 2 * T : T;
   if (v.empty()) v.push_back({0, 0, 0, 0, -1, -1});  // keep the allocation non-empty; the launch is skipped
-  MB_CUDA(cudaMallocAsync(d_tiles, sizeof(TileCoord) * v.size(), stream));
+  MB_CUDA(pool_alloc(d_tiles, sizeof(TileCoord) * v.size(), stream));
   MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice,
                           stream));
   MB_CUDA(cudaStreamSynchronize(stream));  // v goes out of scope
@@ -413,7 +414,22 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
 // Work items one launch keeps in flight: CTAs (one per SM) or CTA pairs (clusters of 2).
 int crossprod_tc_units(int sm_count, int pair) {
   if (!pair) return sm_count;
-  static int clusters = -1;
+  // cached per device: the shared-memory opt-in and the cluster occupancy are device properties
+  // (one process may drive several devices, multi.cu / crossprod_host.cu)
+  static std::atomic<int> cache[64];
+  static std::atomic<bool> cache_init{false};
+  static std::mutex mu;
+  int device = 0;
+  cudaGetDevice(&device);
+  const bool cached_dev = device >= 0 && device < 64;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!cache_init.load()) {
+      for (int i = 0; i < 64; i++) cache[i].store(-1);
+      cache_init.store(true);
+    }
+  }
+  int clusters = cached_dev ? cache[device].load() : -1;
   if (clusters < 0) {
     cudaFuncSetAttribute(crossprod_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
     cudaLaunchConfig_t cfg = {};
@@ -433,6 +449,7 @@ int crossprod_tc_units(int sm_count, int pair) {
       n = 0;
     }
     clusters = n < sm_count / 2 ? n : sm_count / 2;
+    if (cached_dev) cache[device].store(clusters);
   }
   return clusters;
 }
@@ -454,7 +471,7 @@ int crossprod_tc_launch(const int8_t *X8, long rows_pad, long kcols, long pitch,
   if (num_tail > 0) {
     if (!finish || !finish->kind) return fail(-2, __func__, __LINE__, "split tail needs a finishing epilogue");
     const size_t bytes = sizeof(int) * (size_t)num_tail * TC_BM * TC_BN;
-    MB_CUDA(cudaMallocAsync(&scratch, bytes, stream));
+    MB_CUDA(pool_alloc(&scratch, bytes, stream));
     MB_CUDA(cudaMemsetAsync(scratch, 0, bytes, stream));
     fin.tail = scratch;
   }

@@ -45,12 +45,23 @@ colmax_kernel(const double *__restrict__ B, long ldb, long k, unsigned long long
   const int col = blockIdx.x;
   const double *b = B + (size_t)col * ldb;
   double m = 0.0;
-  for (long j = (long)blockIdx.y * 256 + threadIdx.x; j < k; j += (long)gridDim.y * 256)
-    m = fmax(m, fabs(b[j]));
+  bool bad = false;  // NaN or Inf: fmax would drop a NaN silently
+  for (long j = (long)blockIdx.y * 256 + threadIdx.x; j < k; j += (long)gridDim.y * 256) {
+    const double a = fabs(b[j]);
+    m = fmax(m, a);
+    bad |= !(a <= 1.7976931348623157e308);
+  }
   for (int o = 16; o; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (__any_sync(0xffffffffu, bad)) m = __longlong_as_double(0x7ff0000000000000ll);  // +inf marks the column
   // non-negative doubles order like their bit patterns
   if ((threadIdx.x & 31) == 0) atomicMax(&amax[col], (unsigned long long)__double_as_longlong(m));
 }
+
+// A column of B with a NaN / Inf entry has no fixed-point image: its exponent is this marker, its
+// digits are zero and the main kernel's epilogue adds NaN to every row of that column of C (what
+// the reference's fp64 FMA chain yields: 0 * NaN = NaN, dgemm_compressed_cuda.h:253-268).
+constexpr int DT_BAD_EXP = -(1 << 30);
+constexpr unsigned long long DT_INF_BITS = 0x7ff0000000000000ull;
 
 // One thread per k; writes S*ncols rows of Bq (coalesced along k).  Rows >= ncols*S and the
 // K padding stay as initialised (zero).
@@ -62,10 +73,11 @@ quantize_kernel(const double *__restrict__ B, long ldb, long k, int ncols, int S
   const long j = (long)blockIdx.x * 256 + threadIdx.x;
   const int P = 8 * S - 2;
   for (int c = 0; c < ncols; c++) {
-    const double am = __longlong_as_double((long long)amax[c]);
+    const bool finite = amax[c] < DT_INF_BITS;
+    const double am = finite ? __longlong_as_double((long long)amax[c]) : 0.0;
     int e = 0;
     if (am > 0.0) frexp(am, &e);  // am = m 2^e, m in [0.5, 1)  ->  am < 2^e
-    if (j == 0) exps[c] = e;
+    if (j == 0) exps[c] = finite ? e : DT_BAD_EXP;
     if (j < k) {
       const double b = B[j + (size_t)c * ldb];
       long long q = am > 0.0 ? llrint(scalbn(b, P - e)) : 0;  // |q| <= 2^P
@@ -163,7 +175,11 @@ __device__ __forceinline__ void group_bar_sync(int g) {  // named barrier 1 + g,
   asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
 }
 
-template <bool TRACE>
+// PROBE >= 0 (speed-of-light builds, scripts/probes/sol_probe.sh): COMPILE-TIME bits switch parts
+// of the pipeline off (no clock64 bookkeeping, no run-time branches in the hot loops -- a run-time
+// switch alone cost 7 %): 1 = no tcgen05.st, 2 = no MMAs, 4 = no expansion ALU (the raw words are
+// stored).  Results are garbage; timing only.  PROBE < 0: the product kernel (TRACE: p.dbg bits).
+template <bool TRACE, int PROBE>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
                 const __grid_constant__ CUtensorMap tmap_b, const DtParams p) {
@@ -187,6 +203,7 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.R;
   const int stride = gridDim.x;
+  const int dbg = PROBE >= 0 ? PROBE : (TRACE ? p.dbg : 0);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < DT_RMAX * DT_ZSLOTS; i++) mbar_init(&z_full[i], 1);
@@ -267,7 +284,7 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
             const uint32_t a_tmem = tmem_base + acol0 + (g * DT_ASLOTS + as) * 32;
 #pragma unroll
             for (int k4 = 0; k4 < 4; k4++)  // K = 32 per MMA: 8 TMEM columns of A, 32 B of Bq
-              if (!TRACE || !(p.dbg & 2))
+              if (!(dbg & 2))
                 mma_i8_ts(d_tmem, a_tmem + 8 * k4, bdesc + 2 * k4, idesc,
                           (!c.first || sub > 0 || k4 > 0) ? 1u : 0u);
             tc_commit(&ae[as]);
@@ -359,12 +376,24 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
                                    v[2 * sub + 1].x, v[2 * sub + 1].y, v[2 * sub + 1].z,
                                    v[2 * sub + 1].w};
           uint32_t a[32];
+          if (dbg & 4) {
 #pragma unroll
-          for (int qq = 0; qq < 8; qq++)
+            for (int i = 0; i < 32; i++) a[i] = wds[i >> 2];
+          } else {
 #pragma unroll
-            for (int j = 0; j < 4; j++)  // genotype value x 64 as u8: LEFT shifts run on the FMA
-              a[4 * qq + j] = (wds[qq] << (2 * (3 - j))) & 0xC0C0C0C0u;  // pipe (IMAD.SHL)
-          if (!TRACE || !(p.dbg & 1)) tmem_st_32x32b_x32(lane_base + a_col + as * 32, a);
+            for (int qq = 0; qq < 8; qq++)
+#pragma unroll
+              for (int j = 0; j < 4; j++)  // genotype value x 64 as u8: LEFT shifts run on the FMA
+                a[4 * qq + j] = (wds[qq] << (2 * (3 - j))) & 0xC0C0C0C0u;  // pipe (IMAD.SHL)
+          }
+          if (!(dbg & 1)) {
+            tmem_st_32x32b_x32(lane_base + a_col + as * 32, a);
+          } else {  // probe: keep the loads / ALU work alive without the store (never-taken sink)
+            uint32_t x = 0;
+#pragma unroll
+            for (int i = 0; i < 32; i++) x ^= a[i];
+            if (x == 0x9E3779B9u && p.rows < 0) p.C[0] = (double)x;
+          }
           DT_SEG(3)
           tmem_st_wait();
           DT_SEG(4)
@@ -392,8 +421,10 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
             for (int j = 4; j < 8; j++)
               if (j < p.S) hi += (long long)(int)d[j] << (8 * (j - 4));
             const double val = fma((double)hi, 4294967296.0, (double)lo);
+            const int ex = p.exps[col];
             if (row < p.rows)
-              atomicAdd(&p.C[row + (size_t)col * p.ldc], scalbn(val, p.exps[col] - P));
+              atomicAdd(&p.C[row + (size_t)col * p.ldc],
+                        ex == DT_BAD_EXP ? __longlong_as_double(0x7ff8000000000000ll) : scalbn(val, ex - P));
           }
           tc_fence_before();
           __syncwarp();
@@ -436,12 +467,26 @@ __global__ void decide_kernel(const unsigned long long *__restrict__ amaxB,
                               const unsigned long long *__restrict__ amaxC, int n, int P,
                               double rowsum_max, double tol, int *__restrict__ flag) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= n || amaxB[c] == 0ull) return;  // zero column of B: exact
+  if (c >= n || amaxB[c] == 0ull || amaxB[c] >= DT_INF_BITS) return;  // zero column: exact; non-finite: NaN column
   int e = 0;
   frexp(__longlong_as_double((long long)amaxB[c]), &e);  // same exponent rule as quantize_kernel
   const double err = scalbn(rowsum_max, e - P - 1);
   const double mc = __longlong_as_double((long long)amaxC[c]);
   if (!(err <= tol * mc)) atomicOr(flag, 1);
+}
+// err[c] = rowsum_max 2^(e_c - P - 1): the bound decide_kernel tests, for a caller that checks it
+// against the REDUCED result of several shards (multi.cu)
+__global__ void errbound_kernel(const unsigned long long *__restrict__ amaxB, int n, int P,
+                                double rowsum_max, double *__restrict__ err) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  double v = 0.0;
+  if (amaxB[c] != 0ull && amaxB[c] < DT_INF_BITS) {
+    int e = 0;
+    frexp(__longlong_as_double((long long)amaxB[c]), &e);
+    v = scalbn(rowsum_max, e - P - 1);
+  }
+  err[c] = v;
 }
 // amax_all[c] = max(amax_all[c], amax[c]) over the K ranges of one call
 __global__ void amax_merge_kernel(const unsigned long long *__restrict__ amax,
@@ -474,24 +519,45 @@ static int *tc_flag(Handle *h) { return reinterpret_cast<int *>(h->d_w + 8 * (h-
 
 struct TcEnv {
   bool trace = false;
+  int probe = -1;  // MB200_PROBE=bits: launch the speed-of-light instantiation with these bits
   double tol = 5e-11;
   int flags = 0, dbg = 0;
 };
 static const TcEnv &tc_env() {
-  static TcEnv env;
-  static bool init = false;
-  if (!init) {
-    init = true;
-    cudaFuncSetAttribute(dgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         dt_smem_bytes(DT_NMAX));
-    cudaFuncSetAttribute(dgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         dt_smem_bytes(DT_NMAX));
-    if (const char *e = getenv("MB200_TRACE")) env.trace = atoi(e) > 0;
-    if (const char *e = getenv("MB200_DGEMM_TOL")) env.tol = atof(e) > 0 ? atof(e) : env.tol;
-    if (const char *e = getenv("MB200_TC_FLAGS")) env.flags = atoi(e);
-    if (const char *e = getenv("MB200_DBG")) env.dbg = atoi(e);
-  }
+  static const TcEnv env = [] {  // thread-safe one-time init (multi.cu calls from one thread per device)
+    TcEnv v;
+    if (const char *e = getenv("MB200_TRACE")) v.trace = atoi(e) > 0;
+    if (const char *e = getenv("MB200_DBG")) v.dbg = atoi(e);
+    if (const char *e = getenv("MB200_PROBE")) v.probe = atoi(e) & 7;
+    if (const char *e = getenv("MB200_DGEMM_TOL")) v.tol = atof(e) > 0 ? atof(e) : v.tol;
+    if (const char *e = getenv("MB200_TC_FLAGS")) v.flags = atoi(e);
+    return v;
+  }();
   return env;
+}
+
+// The >48 KB dynamic shared memory opt-in is a per-DEVICE function attribute: set it once on every
+// device this process launches the kernel on (single-process multi-GPU handles, multi.cu).
+typedef void (*DtKernel)(CUtensorMap, CUtensorMap, DtParams);
+static DtKernel dt_probe_kernel(int bits) {
+  static const DtKernel k[8] = {dgemm_tc_kernel<false, 0>, dgemm_tc_kernel<false, 1>,
+                                dgemm_tc_kernel<false, 2>, dgemm_tc_kernel<false, 3>,
+                                dgemm_tc_kernel<false, 4>, dgemm_tc_kernel<false, 5>,
+                                dgemm_tc_kernel<false, 6>, dgemm_tc_kernel<false, 7>};
+  return k[bits & 7];
+}
+static int tc_prepare_device(int device) {
+  static std::atomic<unsigned long long> done{0};
+  if (device >= 0 && device < 64 && (done.load(std::memory_order_acquire) >> device & 1ull)) return 0;
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               dt_smem_bytes(DT_NMAX)));
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               dt_smem_bytes(DT_NMAX)));
+  for (int b = 0; b < 8; b++)
+    MB_CUDA(cudaFuncSetAttribute(dt_probe_kernel(b), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 dt_smem_bytes(DT_NMAX)));
+  if (device >= 0 && device < 64) done.fetch_or(1ull << device, std::memory_order_release);
+  return 0;
 }
 
 // One product on a view at S digits per column: centring term into C, then per column group
@@ -551,8 +617,11 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
     const int grid = (int)(units < h->sm_count ? units : h->sm_count);
     if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
     *first_main = false;
-    if (env.trace) dgemm_tc_kernel<true><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
-    else dgemm_tc_kernel<false><<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+    MB_CHECK(tc_prepare_device(h->device));
+    void (*kern)(CUtensorMap, CUtensorMap, DtParams) = dgemm_tc_kernel<false, -1>;
+    if (env.trace) kern = dgemm_tc_kernel<true, -1>;
+    else if (env.probe >= 0) kern = dt_probe_kernel(env.probe);
+    kern<<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
     count_launch();
     MB_LAUNCH_CHECK();
   }
@@ -567,7 +636,12 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
 // Digit count.  Fixed (3..8) when asked for; otherwise adaptive: 8 digits where they cost
 // nothing (n <= 2 fills one 16-row MMA either way; small problems), else 6 digits, verified
 // against a rigorous bound and redone with 8 digits if the bound fails.
+int dgemm_tc_choose_digits(int n, long rows, long K, bool *adaptive);
+double dgemm_tc_tolerance() { return tc_env().tol; }
 static int tc_digits(int n, long rows, long K, bool *adaptive) {
+  return dgemm_tc_choose_digits(n, rows, K, adaptive);
+}
+int dgemm_tc_choose_digits(int n, long rows, long K, bool *adaptive) {
   int S = options().dgemm_slices;
   *adaptive = false;
   if (S == 0) {
@@ -623,7 +697,7 @@ int dgemm_tc_device(Handle *h, int trans, int n, const double *dB, long ldb, dou
 // (rare) redoes the whole product with 8 digits, unchunked.
 // ---------------------------------------------------------------------------------------------
 int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
-                            long ldc, int b_dev, int c_dev) {
+                            long ldc, int b_dev, int c_dev, const TcExternal *ext) {
   MB_CHECK(ensure_bq(h));
   const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
   // panels that already live on the device are used in place; only host panels are copied
@@ -633,9 +707,19 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   const long ldC = c_dev ? ldc : m;
   const bool pipe_in = !trans && !b_dev;   // snps x n panel B uploaded in chunks
   const bool pipe_out = trans && !c_dev;   // snps x n panel C downloaded in chunks
+  // Pageable caller memory (what the reference's bindings pass) goes through the handle's pinned
+  // ring: cudaMemcpyAsync on it would block the host for the whole copy and serialise the chunks.
+  const bool b_pin = !b_dev && host_is_pinned(B), c_pin = !c_dev && host_is_pinned(C);
+  Stager *sg = &h->stager;
+  if ((!b_dev && !b_pin) || (!c_dev && !c_pin)) MB_CHECK(sg->init(4u << 20));
   const DgemmView full = full_view(h, trans);
   bool adaptive = false, first_main = true;
-  const int S = tc_digits(n, full.rows, full.K, &adaptive);
+  int S = tc_digits(n, full.rows, full.K, &adaptive);
+  if (ext) {  // the caller fixes the digits for the whole (sharded) matrix and checks the bound itself
+    if (trans || !c_dev) return fail(-2, __func__, __LINE__, "external check: 'N' with C on the device only");
+    S = ext->S < 3 ? 3 : ext->S > 8 ? 8 : ext->S;
+    adaptive = false;
+  }
   const int ev = (int)(h->ev_count % Handle::kEvRing);
   h->ev_trans[ev] = trans;
   h->last_slices = S;
@@ -674,22 +758,14 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   int *h_flag = reinterpret_cast<int *>(h->h_pipe);
   *h_flag = 0;
   MB_CUDA(cudaMemsetAsync(tc_flag(h), 0, sizeof(int), h->stream));
-  auto copy2d = [](void *dst, long dld, const void *src, long sld, long rows, int cols,
-                   cudaMemcpyKind kind, cudaStream_t st) {
-    if (dld == rows && sld == rows)
-      return cudaMemcpyAsync(dst, src, sizeof(double) * rows * cols, kind, st);
-    return cudaMemcpy2DAsync(dst, sizeof(double) * dld, src, sizeof(double) * sld,
-                             sizeof(double) * rows, cols, kind, st);
-  };
 
-  if (!b_dev && !pipe_in)
-    MB_CUDA(copy2d(h->d_B, k, B, ldb, k, n, cudaMemcpyHostToDevice, h->stream));
+  if (!b_dev && !pipe_in) MB_CHECK(panel_h2d(sg, b_pin, h->d_B, k, B, ldb, k, n, h->stream));
   if (!trans) {
     MB_CUDA(cudaMemsetAsync(tc_amax_all(h), 0, sizeof(unsigned long long) * n, h->stream));
     for (int i = 0; i < chunks; i++) {
       const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
-      if (pipe_in) {
-        MB_CUDA(copy2d(h->d_B + s0, k, B + s0, ldb, cnt, n, cudaMemcpyHostToDevice, h->copy_stream));
+      if (pipe_in) {  // staged uploads block the host while the kernels of chunk i-1 run
+        MB_CHECK(panel_h2d(sg, b_pin, h->d_B + s0, k, B + s0, ldb, cnt, n, h->copy_stream));
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
         MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
       }
@@ -698,7 +774,20 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
       MB_CHECK(tc_pass(h, v, n, dB + s0, ldB, dC, ldC, S, 0, nullptr, tc_amax_all(h), &first_main, ev));
     }
     if (adaptive) MB_CHECK(tc_check(h, dC, ldC, m, n, S, tc_amax_all(h), full.rowsum_max));
+    if (ext && ext->d_err) {
+      errbound_kernel<<<(unsigned)ceil_div(n, 64), 64, 0, h->stream>>>(tc_amax_all(h), n, 8 * S - 2,
+                                                                       full.rowsum_max, ext->d_err);
+      count_launch();
+      MB_LAUNCH_CHECK();
+    }
   } else {
+    // the download of chunk i-1 is enqueued AFTER the kernels of chunk i: a staged download blocks
+    // the host until its slots have drained, and the GPU must have the next kernels by then
+    auto download = [&](int i) -> int {
+      const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
+      MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
+      return panel_d2h(sg, c_pin, C + s0, ldc, dC + s0, ldC, cnt, n, h->copy_stream);
+    };
     for (int i = 0; i < chunks; i++) {
       const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
       const DgemmView v = sub_view(h, 1, s0, cnt);
@@ -707,23 +796,27 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
         MB_CHECK(tc_check(h, dC + s0, ldC, cnt, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
       if (pipe_out) {
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->stream));
-        MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
-        MB_CUDA(copy2d(C + s0, ldc, dC + s0, ldC, cnt, n, cudaMemcpyDeviceToHost, h->copy_stream));
+        if (i > 0) MB_CHECK(download(i - 1));
       }
     }
+    if (pipe_out) MB_CHECK(download(chunks - 1));
   }
-  if (!c_dev && !pipe_out)
-    MB_CUDA(copy2d(C, ldc, dC, ldC, m, n, cudaMemcpyDeviceToHost, h->stream));
+  if (!c_dev && !pipe_out) MB_CHECK(panel_d2h(sg, c_pin, C, ldc, dC, ldC, m, n, h->stream));
   if (adaptive)
     MB_CUDA(cudaMemcpyAsync(h_flag, tc_flag(h), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
   h->ev_count++;
+  if (ext && ext->no_sync) return 0;
+  if (!c_dev && !c_pin) MB_CHECK(sg->drain());  // staged downloads reach the caller's memory here
   MB_CUDA(cudaStreamSynchronize(h->stream));
   MB_CUDA(cudaStreamSynchronize(h->copy_stream));
   if (adaptive && *h_flag) {  // bound failed somewhere: exact-to-2^-62 redo, everything resident
     first_main = false;
     MB_CHECK(tc_pass(h, full, n, dB, ldB, dC, ldC, 8, 1, nullptr, nullptr, &first_main, ev));
-    if (!c_dev) MB_CUDA(copy2d(C, ldc, dC, ldC, m, n, cudaMemcpyDeviceToHost, h->stream));
+    if (!c_dev) {
+      MB_CHECK(panel_d2h(sg, c_pin, C, ldc, dC, ldC, m, n, h->stream));
+      if (!c_pin) MB_CHECK(sg->drain());
+    }
     MB_CUDA(cudaStreamSynchronize(h->stream));
     h->last_slices = 8;
   }

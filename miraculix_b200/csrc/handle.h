@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <vector>
+#include "stager.h"
 
 namespace mb200 {
 
@@ -55,8 +56,7 @@ struct Handle {
   void *d_cg = nullptr;    // conjugate-gradient workspace (solver.cu), allocated on first use
   size_t cg_bytes = 0;
   void *h_cg = nullptr;    // pinned scalars the solver's kernels write for the host
-  void *pinned = nullptr;  // pinned staging for host<->device copies of B / C
-  size_t pinned_bytes = 0;
+  Stager stager;           // pinned ring for pageable caller panels (stager.h), created on first use
   cudaStream_t stream = nullptr;
   // host-pointer dgemm_compressed pipelines the PCIe copies of B / C against the kernels:
   cudaStream_t copy_stream = nullptr;
@@ -87,19 +87,35 @@ DgemmView full_view(const Handle *h, int trans);
 DgemmView sub_view(const Handle *h, int trans, long begin, long count);  // SNP range [begin, begin+count)
 
 Handle *as_handle(void *p);  // validates magic, sets device; nullptr + status on failure
+// device < 0: CUDA_DEVICE / the calling thread's current device (select_device)
+int create_handle(long snps, long indiv, int max_n, Handle **out, int device = -1);
+void destroy_handle(Handle *h);
+int repack_from_host(Handle *h, const uint8_t *plink);
+int finish_handle(Handle *h, const double *f_host);  // f (host, or nullptr = from counts) + row-sum maxima
 
 // repack.cu
 int repack_from_device(Handle *h, const uint8_t *d_plink);  // d_plink: [snps][ceil(indiv/4)]
+// rows [s_offset, s_offset + snps) of the simulated matrix with this seed (shards of one matrix)
 int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long seed,
-                   cudaStream_t stream);
+                   cudaStream_t stream, long s_offset = 0);
 int freq_from_counts(Handle *h);  // d_f = counts / (2 indiv)
 int rowsum_maxima(Handle *h);     // fills h->rowsum_max (synchronises the stream)
 
 // dgemm.cu
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
+// SNP-sharded 'N' (multi.cu): the digit count is fixed by the caller for the whole matrix and the
+// a-posteriori check needs the REDUCED result, so the shard only reports the rigorous bound of its
+// partial: d_err[c] = rowsum_max 2^(e_c - P - 1) (0 for a zero column).
+struct TcExternal {
+  int S = 0;                // digits per column (3..8)
+  double *d_err = nullptr;  // device, n doubles
+  bool no_sync = false;     // leave the handle's stream running (the caller orders what follows on it)
+};
 // Host panels B, C: copies pipelined against the kernels in SNP chunks (dgemm_tc.cu)
 int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long ldb, double *C,
-                            long ldc, int b_dev, int c_dev);
+                            long ldc, int b_dev, int c_dev, const TcExternal *ext = nullptr);
+int dgemm_tc_choose_digits(int n, long rows, long K, bool *adaptive);  // the policy of mb200_set_dgemm_mode
+double dgemm_tc_tolerance();
 
 int dgemm_tc_read_trace(long long *out, int n);
 int dgemm_tc_last_precision(Handle *h, int *slices);  // dgemm_tc.cu, MB200_TRACE=1
@@ -130,6 +146,10 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
                      CrossprodTiming *timing);
 
 long crossprod_partition_rows(long rows, int part, int nparts);
+int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int part,
+                               int nparts, int32_t *C32, cudaStream_t stream, double *executed_ops);
+int crossprod_row_sums(const uint8_t *d_x, long k, long rows, int is_plink_format, const double *d_f,
+                       int do_scale, double *d_m, cudaStream_t stream);
 int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
                                const double *d_f, int do_scale, int part, int nparts,
                                double *d_panel, cudaStream_t stream, CrossprodTiming *timing);

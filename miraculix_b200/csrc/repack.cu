@@ -273,13 +273,18 @@ repack_fast_kernel(const uint32_t *__restrict__ plink, long s_begin, long s_coun
 
 int repack_chunk(Handle *h, const uint8_t *d_chunk, long s_begin, long s_count) {
   const long bs = ceil_div(h->indiv, 4);
-  static int use_fast = -1;
-  if (use_fast < 0) {
+  static const int use_fast = [] {
     const char *e = getenv("MB200_REPACK_FAST");
-    use_fast = e ? atoi(e) : 1;
-    cudaFuncSetAttribute(repack_fast_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
-    cudaFuncSetAttribute(repack_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
-    cudaFuncSetAttribute(repack_fast_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM);
+    return e ? atoi(e) : 1;
+  }();
+  {  // the > 48 KB dynamic shared memory opt-in is per device
+    static std::atomic<unsigned long long> done{0};
+    if (h->device < 0 || h->device >= 64 || !(done.load(std::memory_order_acquire) >> h->device & 1ull)) {
+      MB_CUDA(cudaFuncSetAttribute(repack_fast_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM));
+      MB_CUDA(cudaFuncSetAttribute(repack_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM));
+      MB_CUDA(cudaFuncSetAttribute(repack_fast_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_SMEM));
+      if (h->device >= 0 && h->device < 64) done.fetch_or(1ull << h->device, std::memory_order_release);
+    }
   }
   if (use_fast && bs % 4 == 0 && (reinterpret_cast<uintptr_t>(d_chunk) & 3) == 0 &&
       s_begin % RF_TILE == 0) {
@@ -405,13 +410,13 @@ __device__ __forceinline__ uint64_t mix64(uint64_t x) {  // splitmix64 finaliser
 }
 __global__ void __launch_bounds__(256)
 simulate_kernel(uint8_t *__restrict__ plink, long snps, long indiv, long bs,
-                unsigned long long seed) {
+                unsigned long long seed, long s_offset) {
   const long total_words = snps * ((bs + 3) / 4);
   const long wpr = (bs + 3) / 4;  // 32-bit words per row (last one partial)
   for (long w = (long)blockIdx.x * blockDim.x + threadIdx.x; w < total_words;
        w += (long)gridDim.x * blockDim.x) {
     const long s = w / wpr, wb = w % wpr;
-    const uint64_t ks = mix64(seed ^ (0xA5A5A5A5ull + (uint64_t)s * 0x100000001B3ull));
+    const uint64_t ks = mix64(seed ^ (0xA5A5A5A5ull + (uint64_t)(s + s_offset) * 0x100000001B3ull));
     const uint32_t thr = (uint32_t)((0.1 + 0.5 * ((ks >> 11) * (1.0 / 9007199254740992.0))) *
                                     4294967296.0);
     uint32_t word = 0;
@@ -437,9 +442,11 @@ simulate_kernel(uint8_t *__restrict__ plink, long snps, long indiv, long bs,
   }
 }
 int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long seed,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, long s_offset) {
   const long bs = ceil_div(indiv, 4);
-  simulate_kernel<<<148 * 8, 256, 0, stream>>>(d_plink, snps, indiv, bs, seed);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  simulate_kernel<<<device_sm_count(dev) * 8, 256, 0, stream>>>(d_plink, snps, indiv, bs, seed, s_offset);
   count_launch();
   MB_LAUNCH_CHECK();
   return 0;

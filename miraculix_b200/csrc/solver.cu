@@ -16,6 +16,7 @@
 #include "../../include/miraculix_b200.h"
 #include "common.cuh"
 #include "handle.h"
+#include "multi.h"
 
 namespace mb200 {
 
@@ -223,7 +224,12 @@ int mb200_cg_solve_device(void *compressed, const double *d_b, double *d_x, doub
 
 int mb200_cg_solve(void *compressed, const double *b, double *x, double lambda, double tol,
                    int max_iter, int *iters, double *resid_norm) {
+  MB_RANGE();
   clear_status();
+  if (MultiHandle *m = as_multi(compressed)) {
+    if (!b || !x || max_iter < 0) return fail(-2, __func__, __LINE__, "bad arguments");
+    return multi_cg_solve(m, b, x, lambda, tol, max_iter, iters, resid_norm);
+  }
   Handle *h = as_handle(compressed);
   if (!h) return status().code;
   if (!b || !x || max_iter < 0) return fail(-2, __func__, __LINE__, "bad arguments");

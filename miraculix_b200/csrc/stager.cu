@@ -1,0 +1,292 @@
+// stager.cu -- pinned staging ring + host copy pool for pageable caller memory (see stager.h).
+#include "stager.h"
+#include <stdlib.h>
+#include <string.h>
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+#include <vector>
+#include "common.cuh"
+
+namespace mb200 {
+
+// ---------------------------------------------------------------------------------------------
+// Copy pool: helper threads that take slices of one 2-D copy.  Several device worker threads
+// (multi.cu) may call parallel_copy_2d at the same time; calls are serialised on the pool (the
+// helpers are a shared resource: memory bandwidth, not core count, is what they multiply).
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct CopyJob {
+  uint8_t *dst = nullptr;
+  const uint8_t *src = nullptr;
+  size_t dpitch = 0, spitch = 0, width = 0, height = 0;
+  size_t pieces = 0, piece_bytes = 0;  // the flattened width*height bytes are cut into pieces
+  std::atomic<size_t> next{0}, done{0};
+};
+
+void copy_piece(const CopyJob &j, size_t piece) {
+  size_t b0 = piece * j.piece_bytes;
+  const size_t total = j.width * j.height;
+  size_t b1 = b0 + j.piece_bytes < total ? b0 + j.piece_bytes : total;
+  while (b0 < b1) {  // a piece may span several columns
+    const size_t col = b0 / j.width, off = b0 % j.width;
+    const size_t n = j.width - off < b1 - b0 ? j.width - off : b1 - b0;
+    memcpy(j.dst + col * j.dpitch + off, j.src + col * j.spitch + off, n);
+    b0 += n;
+  }
+}
+
+class CopyPool {
+ public:
+  static CopyPool &get() {
+    static CopyPool pool;
+    return pool;
+  }
+  int helpers() const { return (int)threads_.size(); }
+  void run(CopyJob &job) {
+    std::lock_guard<std::mutex> call(call_mu_);  // one 2-D copy at a time uses the helpers
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      job_ = &job;
+      gen_++;
+    }
+    cv_.notify_all();
+    work(job);
+    // wait until every piece is done AND every helper has left the job
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [&] { return job.done.load() == job.pieces && active_ == 0; });
+    job_ = nullptr;
+  }
+
+ private:
+  CopyPool() {
+    int n = 0;
+    if (const char *e = getenv("MB200_COPY_THREADS")) n = atoi(e);
+    else {
+      const unsigned hw = std::thread::hardware_concurrency();
+      n = (int)(hw / 2);
+      if (n > 8) n = 8;
+      n -= 1;  // the caller copies too
+    }
+    if (n < 0) n = 0;
+    for (int i = 0; i < n; i++) threads_.emplace_back([this] { loop(); });
+  }
+  ~CopyPool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      quit_ = true;
+    }
+    cv_.notify_all();
+    for (auto &t : threads_) t.join();
+  }
+  static void work(CopyJob &job) {
+    for (;;) {
+      const size_t p = job.next.fetch_add(1);
+      if (p >= job.pieces) break;
+      copy_piece(job, p);
+      job.done.fetch_add(1);
+    }
+  }
+  void loop() {
+    unsigned long long seen = 0;
+    for (;;) {
+      CopyJob *job = nullptr;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return quit_ || gen_ != seen; });
+        if (quit_) return;
+        seen = gen_;
+        job = job_;
+        if (job) active_++;
+      }
+      if (!job) continue;
+      work(*job);
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        active_--;
+      }
+      done_cv_.notify_all();
+    }
+  }
+  std::vector<std::thread> threads_;
+  std::mutex mu_, call_mu_;
+  std::condition_variable cv_, done_cv_;
+  CopyJob *job_ = nullptr;
+  unsigned long long gen_ = 0;
+  int active_ = 0;
+  bool quit_ = false;
+};
+
+}  // namespace
+
+void parallel_copy_2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                      size_t height) {
+  if (!width || !height) return;
+  const size_t total = width * height;
+  CopyJob job;
+  job.dst = static_cast<uint8_t *>(dst);
+  job.src = static_cast<const uint8_t *>(src);
+  job.dpitch = dpitch;
+  job.spitch = spitch;
+  job.width = width;
+  job.height = height;
+  constexpr size_t kMinPiece = 256 << 10;  // below ~256 KB per thread the hand-off costs more
+  CopyPool &pool = CopyPool::get();
+  const size_t parts = (size_t)pool.helpers() + 1;
+  if (parts == 1 || total < 2 * kMinPiece) {
+    job.pieces = 1;
+    job.piece_bytes = total;
+    copy_piece(job, 0);
+    return;
+  }
+  size_t pieces = total / kMinPiece;
+  if (pieces > 4 * parts) pieces = 4 * parts;
+  job.piece_bytes = ((total + pieces - 1) / pieces + 63) & ~(size_t)63;
+  job.pieces = (total + job.piece_bytes - 1) / job.piece_bytes;
+  pool.run(job);
+}
+
+bool host_is_pinned(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stager
+// ---------------------------------------------------------------------------------------------
+int Stager::init(size_t slot_bytes_) {
+  if (ring) return 0;
+  slot_bytes = slot_bytes_;
+  MB_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&ring), kSlots * slot_bytes, cudaHostAllocPortable));
+  for (int i = 0; i < kSlots; i++) MB_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+  return 0;
+}
+
+void Stager::destroy() {
+  if (ring) cudaFreeHost(ring);
+  ring = nullptr;
+  for (int i = 0; i < kSlots; i++) {
+    if (done[i]) cudaEventDestroy(done[i]);
+    done[i] = nullptr;
+    busy[i] = false;
+    pend[i].on = false;
+  }
+}
+
+// The slot's last DMA is over; a pending download leaves for the caller's memory.
+int Stager::retire(int slot) {
+  if (!busy[slot]) return 0;
+  MB_CUDA(cudaEventSynchronize(done[slot]));
+  busy[slot] = false;
+  Pending &p = pend[slot];
+  if (p.on) {
+    p.on = false;
+    parallel_copy_2d(p.dst, sizeof(double) * p.ld, ring + (size_t)slot * slot_bytes,
+                     sizeof(double) * p.rows, sizeof(double) * p.rows, (size_t)p.cols);
+  }
+  return 0;
+}
+
+int Stager::acquire(int *slot) {
+  const int s = next;
+  next = (next + 1) % kSlots;
+  MB_CHECK(retire(s));
+  *slot = s;
+  return 0;
+}
+
+int Stager::drain() {
+  for (int i = 0; i < kSlots; i++) MB_CHECK(retire((next + i) % kSlots));  // oldest first
+  return 0;
+}
+
+int Stager::upload(double *d, long ld_d, const double *h, long ld_h, long rows, int cols,
+                   cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  const long slot_rows = (long)(slot_bytes / sizeof(double));
+  const long rp_max = rows < slot_rows ? rows : slot_rows;
+  for (long r0 = 0; r0 < rows; r0 += rp_max) {
+    const long rp = rows - r0 < rp_max ? rows - r0 : rp_max;
+    int cps = (int)(slot_rows / rp);  // whole columns per slot
+    if (cps < 1) cps = 1;
+    for (int c0 = 0; c0 < cols; c0 += cps) {
+      const int nc = cols - c0 < cps ? cols - c0 : cps;
+      int slot = 0;
+      MB_CHECK(acquire(&slot));
+      uint8_t *buf = ring + (size_t)slot * slot_bytes;
+      parallel_copy_2d(buf, sizeof(double) * rp, h + r0 + (size_t)c0 * ld_h, sizeof(double) * ld_h,
+                       sizeof(double) * rp, (size_t)nc);
+      MB_CUDA(cudaMemcpy2DAsync(d + r0 + (size_t)c0 * ld_d, sizeof(double) * ld_d, buf,
+                                sizeof(double) * rp, sizeof(double) * rp, (size_t)nc,
+                                cudaMemcpyHostToDevice, st));
+      MB_CUDA(cudaEventRecord(done[slot], st));
+      busy[slot] = true;
+    }
+  }
+  return 0;
+}
+
+int Stager::download(double *h, long ld_h, const double *d, long ld_d, long rows, int cols,
+                     cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  const long slot_rows = (long)(slot_bytes / sizeof(double));
+  const long rp_max = rows < slot_rows ? rows : slot_rows;
+  for (long r0 = 0; r0 < rows; r0 += rp_max) {
+    const long rp = rows - r0 < rp_max ? rows - r0 : rp_max;
+    int cps = (int)(slot_rows / rp);
+    if (cps < 1) cps = 1;
+    for (int c0 = 0; c0 < cols; c0 += cps) {
+      const int nc = cols - c0 < cps ? cols - c0 : cps;
+      int slot = 0;
+      MB_CHECK(acquire(&slot));  // may complete an older download of this ring first
+      uint8_t *buf = ring + (size_t)slot * slot_bytes;
+      MB_CUDA(cudaMemcpy2DAsync(buf, sizeof(double) * rp, d + r0 + (size_t)c0 * ld_d,
+                                sizeof(double) * ld_d, sizeof(double) * rp, (size_t)nc,
+                                cudaMemcpyDeviceToHost, st));
+      MB_CUDA(cudaEventRecord(done[slot], st));
+      busy[slot] = true;
+      pend[slot].on = true;
+      pend[slot].dst = h + r0 + (size_t)c0 * ld_h;
+      pend[slot].ld = ld_h;
+      pend[slot].rows = rp;
+      pend[slot].cols = nc;
+    }
+  }
+  return 0;
+}
+
+static cudaError_t copy2d_direct(void *dst, long dld, const void *src, long sld, long rows, int cols,
+                                 cudaMemcpyKind kind, cudaStream_t st) {
+  if (dld == rows && sld == rows)
+    return cudaMemcpyAsync(dst, src, sizeof(double) * rows * cols, kind, st);
+  return cudaMemcpy2DAsync(dst, sizeof(double) * dld, src, sizeof(double) * sld, sizeof(double) * rows,
+                           (size_t)cols, kind, st);
+}
+
+int panel_h2d(Stager *sg, bool pinned, double *d, long ld_d, const double *h, long ld_h, long rows,
+              int cols, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  if (pinned || !sg || !sg->ring) {
+    MB_CUDA(copy2d_direct(d, ld_d, h, ld_h, rows, cols, cudaMemcpyHostToDevice, st));
+    return 0;
+  }
+  return sg->upload(d, ld_d, h, ld_h, rows, cols, st);
+}
+
+int panel_d2h(Stager *sg, bool pinned, double *h, long ld_h, const double *d, long ld_d, long rows,
+              int cols, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  if (pinned || !sg || !sg->ring) {
+    MB_CUDA(copy2d_direct(h, ld_h, d, ld_d, rows, cols, cudaMemcpyDeviceToHost, st));
+    return 0;
+  }
+  return sg->download(h, ld_h, d, ld_d, rows, cols, st);
+}
+
+}  // namespace mb200
