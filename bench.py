@@ -6,8 +6,12 @@ Metric (BASELINE.json): dgemm_compressed throughput in SNP*indiv*col/s on config
 ("strong" scaling: the total matrix is fixed; 't' needs no exchange, 'n' is followed by one NCCL
 all-reduce of the indiv x ncol partials).  A "step" = one 'n' call + one 't' call.
 
-  value     device-resident B/C (mb200_dgemm_compressed_device), CUDA events on the library's stream
-  e2e       the reference-facing C-ABI call dgemm_compressed() with pinned HOST B/C, copies inside
+  value     device-resident B/C (mb200_dgemm_compressed_device), CUDA events on the library's stream;
+            N > 1: one process per GPU (torch.distributed / NCCL all-reduce of the 'n' partials)
+  e2e       the reference-facing C-ABI call dgemm_compressed() with HOST B/C, copies inside; N > 1:
+            ONE process (rank 0) drives all N GPUs through the library's single-process multi-device
+            handle (MIRACULIX_NGPUS path, csrc/multi.cu) -- what an unchanged Julia / Fortran caller
+            gets; pinned host panels for the headline, pageable ones beside it (e2e.pageable)
   roofline  dominant kernel's algorithmic HBM bytes / its CUDA-event duration vs MEASURED_PEAKS.json
   cpu_baseline  the unmodified reference CPU 5codes library (oracle/_ref) on a bounded sub-block
   grm       the GRM crossproduct of configs[1] (50k x 10k) in int8 TOPS (second half of the metric)
@@ -54,6 +58,12 @@ def parse_args():
                     help="configs[4] (1M SNPs x 100k individuals GRM over the GPUs): 1 on, 0 off, -1 = on at 8 GPUs")
     ap.add_argument("--grm-full-snps", type=int, default=1_000_000)
     ap.add_argument("--grm-full-indiv", type=int, default=100_000)
+    ap.add_argument("--no-small", action="store_true", help="skip the configs[0] latency leg")
+    ap.add_argument("--wide-ncol", type=int, default=50,
+                    help="extra leg: 'n'+'t' with this many columns (gblup PCA shape); 0 = off")
+    ap.add_argument("--e2e-devices", default="",
+                    help="device list of the single-process e2e arm (default 0..N-1; '0,0' exercises the "
+                         "multi-device handle on one GPU)")
     ap.add_argument("--cpu-snps", type=int, default=100_000)
     ap.add_argument("--cpu-indiv", type=int, default=10_000)
     return ap.parse_args()
@@ -204,10 +214,12 @@ def run_ours(args):
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_group = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=dev)
+        # host-side barriers for the phases in which ONE rank drives all GPUs (a NCCL barrier would
+        # park a spinning kernel on every waiting rank's GPU)
+        host_group = dist.new_group(backend="gloo")
     build.build()
     lib = api.load_library()
     api.set_options(use_gpu=True, not_center=False)
@@ -220,8 +232,9 @@ def run_ours(args):
     # synthetic shard, generated on the device (never crosses PCIe), then repacked on the device
     t0 = time.perf_counter()
     bed = torch.empty(s_loc * bs, dtype=torch.uint8, device=dev)
-    api._check(lib.mb200_simulate_plink_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, 1000 + rank),
-               "simulate")
+    SEED = 1000
+    api._check(lib.mb200_simulate_plink_rows_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, SEED,
+                                                    sh.s_begin), "simulate")
     handle = C.c_void_p(None)
     api._check(lib.mb200_plink2compressed_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, None,
                                                  ncol, C.byref(handle)), "plink2compressed_device")
@@ -232,12 +245,13 @@ def run_ours(args):
     sh.handle = handle
     stream = sh.stream()
 
-    g = torch.Generator(device=dev)
-    g.manual_seed(7)
-    Bn_full = torch.randn((ncol, snps), dtype=torch.float64, device=dev, generator=g)
-    Bn = Bn_full[:, sh.s_begin:sh.s_begin + s_loc].contiguous()   # this rank's rows of B
-    del Bn_full
-    Bt = torch.randn((ncol, indiv), dtype=torch.float64, device=dev, generator=g)
+    # B panels: generated once on the host (seeded), so that the device-resident arm, the sharded
+    # arm and the single-process multi-device arm multiply the same numbers
+    rng = np.random.default_rng(7)
+    hBn_full = torch.from_numpy(rng.standard_normal((ncol, snps))).pin_memory()
+    hBt = torch.from_numpy(rng.standard_normal((ncol, indiv))).pin_memory()
+    Bn = hBn_full[:, sh.s_begin:sh.s_begin + s_loc].contiguous().to(dev)   # this rank's rows of B
+    Bt = hBt.to(dev)
     Cn = torch.empty((ncol, indiv), dtype=torch.float64, device=dev)
     Ct = torch.empty((ncol, s_loc), dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
@@ -281,53 +295,56 @@ def run_ours(args):
     k_n = [ms_arr[i] for i in range(got) if tr_arr[i] == 0]
     k_t = [ms_arr[i] for i in range(got) if tr_arr[i] == 1]
 
-    # ---- e2e: pinned HOST panels, H2D of B and D2H of C inside the timed region ----
-    hBn = torch.randn((ncol, s_loc), dtype=torch.float64).pin_memory()
-    hBt = torch.randn((ncol, indiv), dtype=torch.float64).pin_memory()
-    hCn = torch.empty((ncol, indiv), dtype=torch.float64).pin_memory()
-    hCt = torch.empty((ncol, s_loc), dtype=torch.float64).pin_memory()
+    # results of the device-timed arm, kept for the parity check of the e2e arms below
+    stream.synchronize()
+    Cn_dev, Ct_dev = Cn.cpu(), Ct.cpu()
 
-    def step_e2e():
-        if world == 1:
-            # the reference-facing call itself: dgemm_compressed(trans, handle, n, B, ldb, C, ldc)
-            lib.dgemm_compressed(b"N", handle, ncol, hBn.data_ptr(), snps, hCn.data_ptr(), indiv)
-            lib.dgemm_compressed(b"T", handle, ncol, hBt.data_ptr(), indiv, hCt.data_ptr(), snps)
-        else:
-            sh.dgemm_n_host(hBn, Cn, hCn)   # pipelined upload, device all-reduce, async download
-            sh.dgemm_t_host(hBt, hCt)       # the C-ABI call on the shard, pipelined download
-            stream.synchronize()
-
-    e2e_steps = max(2, min(args.steps, 5))
-    e2e_ms, _ = timed(step_e2e, e2e_steps, 1)
-    if world == 1 and lib.mb200_last_status() != 0:
-        raise SystemExit("dgemm_compressed failed: " + lib.mb200_last_message().decode())
     clocks = None
+    e2e_devices = [int(x) for x in args.e2e_devices.split(",")] if args.e2e_devices else list(range(world))
+    e2e_steps = max(2, min(args.steps, 5))
+
+    def host_barrier():
+        if host_group is not None:
+            dist.barrier(group=host_group)
+
+    # ---- e2e: the reference-facing call with HOST panels, copies inside the timed region.  One
+    # process: at N > 1 rank 0 alone drives all GPUs through a sharded handle of the SAME matrix
+    # (the other ranks keep their contexts but are idle on a host-side barrier).
+    torch.cuda.synchronize()
+    host_barrier()
+    e2e = None
+    if rank == 0:
+        e2e = run_e2e(args, lib, api, handle if len(e2e_devices) == 1 else None, e2e_devices, SEED,
+                      hBn_full, hBt, Cn_dev, Ct_dev, e2e_steps)
+    host_barrier()
     if sampler:
         sampler.stop()
         clocks = ClockSampler.stats(sampler.rows)               # whole run: device-timed + e2e legs
         clocks["device_timed"] = ClockSampler.stats(sampler.rows[mark0:mark1])
+    small = None
+    if rank == 0 and not args.no_small:
+        small = run_small(lib, api)
+    host_barrier()
     pcg = None
     if not args.no_pcg:
-        pcg = run_pcg(args, lib, api, dev, rank, world)
+        pcg = run_pcg(args, lib, api, dev, rank, world, host_barrier, e2e_devices)
     grm_part = None
     if not args.no_grm and world > 1:
         grm_part = run_grm_partition(args, lib, api, dev, rank, world, args.grm_snps, args.grm_indiv,
-                                     "BASELINE configs[1]")
+                                     "BASELINE configs[1]", host_barrier=host_barrier, e2e_devices=e2e_devices)
     grm_full = None
     if not args.no_grm and world > 1 and (args.grm_full == 1 or (args.grm_full < 0 and world == 8)):
         grm_full = run_grm_partition(args, lib, api, dev, rank, world, args.grm_full_snps,
-                                     args.grm_full_indiv, "BASELINE configs[4]", reps=2, warm=1)
+                                     args.grm_full_indiv, "BASELINE configs[4]", reps=2, warm=1,
+                                     host_barrier=host_barrier, e2e_devices=e2e_devices, sampled=True)
 
     units_step = 2.0 * snps * indiv * ncol
     value = units_step * args.steps / (total_ms * 1e-3)
-    e2e_value = units_step * e2e_steps / (e2e_ms * 1e-3)
-    h2d = 8 * ncol * (s_loc + indiv)
-    d2h = 8 * ncol * (indiv + s_loc)
 
     # Tear down in an order that never leaves torch holding events on the library's stream:
     # pinned and device panels first (the host allocator records an event on every stream that
     # used a pinned block), then the process group, then the handle (which destroys the stream).
-    del hBn, hBt, hCn, hCt, Bn, Bt, Cn, Ct
+    del hBn_full, hBt, Bn, Bt, Cn, Ct
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
     if hasattr(torch._C, "_host_emptyCache"):
@@ -375,13 +392,11 @@ def run_ours(args):
                        "dgemm_mode": int(os.environ.get("MB200_DGEMM_MODE", "-1")),
                        "setup_s": setup_s},
             "roofline": roofline,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                    "ms_per_step": e2e_ms / e2e_steps,
-                    "api": "dgemm_compressed() C-ABI with pinned host B/C" if world == 1 else
-                           "ShardedCompressed.dgemm_n_host/dgemm_t_host: pinned host B/C, pipelined PCIe, NCCL all-reduce"},
+            "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks}
 
+    if small is not None:
+        line["small"] = small
     if pcg is not None:
         line["pcg"] = pcg
     if not args.no_grm and world == 1:
@@ -396,6 +411,11 @@ def run_ours(args):
         except Exception as exc:  # the CPU checker must never take the GPU line down
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                                     "sample": f"failed: {exc}"}
+        if isinstance(line.get("small"), dict):
+            try:
+                line["small"]["cpu_baseline"] = run_small_cpu_baseline()
+            except Exception as exc:
+                line["small"]["cpu_baseline"] = {"value": None, "kind": "reference", "sample": f"failed: {exc}"}
         if rank == 0 and world == 1 and isinstance(line.get("grm"), dict):
             try:
                 line["grm"]["cpu_baseline"] = run_grm_cpu_baseline()
@@ -405,7 +425,115 @@ def run_ours(args):
     print(json.dumps(line))
 
 
-def run_pcg(args, lib, api, dev, rank, world):
+
+def _wall_steps(fn, steps, warm):
+    """Wall-clock seconds per call of a BLOCKING host call (the C-ABI entry points return after the
+    result is in host memory), mean and best over `steps` calls after `warm` warm-ups."""
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        fn()
+        ts.append(time.perf_counter() - t0)
+    return sum(ts) / len(ts), min(ts)
+
+
+def run_e2e(args, lib, api, handle, devices, seed, hBn, hBt, Cn_dev, Ct_dev, steps):
+    """dgemm_compressed() 'n' + 't' through the C ABI with host panels, one process.  handle: an
+    existing single-device handle, or None = create a handle of the same simulated matrix over
+    `devices` (the MIRACULIX_NGPUS path).  Pinned panels (headline), pageable panels beside them,
+    and a parity check of both against the device-resident arm's result."""
+    import numpy as np
+    import torch
+    snps, indiv, ncol = args.snps, args.indiv, args.ncol
+    own = handle is None
+    if own:
+        api.set_devices(devices)
+        try:
+            handle = api.simulate_compressed(snps, indiv, seed, ncol)
+        finally:
+            api.set_devices(None)
+    nsh = lib.mb200_shard_count(handle)
+    hCn = torch.empty((ncol, indiv), dtype=torch.float64).pin_memory()
+    hCt = torch.empty((ncol, snps), dtype=torch.float64).pin_memory()
+
+    def call(tr, B, k, Cout, m):
+        lib.dgemm_compressed(tr, handle, ncol, B, k, Cout, m)
+        if lib.mb200_last_status() != 0:
+            raise SystemExit("dgemm_compressed failed: " + lib.mb200_last_message().decode())
+
+    def step_pinned():
+        call(b"N", hBn.data_ptr(), snps, hCn.data_ptr(), indiv)
+        call(b"T", hBt.data_ptr(), indiv, hCt.data_ptr(), snps)
+
+    launches0 = api.kernel_launches()
+    mean_s, best_s = _wall_steps(step_pinned, steps, 2)
+    launches = (api.kernel_launches() - launches0) // (steps + 2)
+    n_s, _ = _wall_steps(lambda: call(b"N", hBn.data_ptr(), snps, hCn.data_ptr(), indiv), steps, 0)
+    t_s, _ = _wall_steps(lambda: call(b"T", hBt.data_ptr(), indiv, hCt.data_ptr(), snps), steps, 0)
+
+    # parity: the e2e result against the device-resident arm (same matrix, same B)
+    def rel(a, b):
+        return float((a - b).abs().max() / b.abs().max())
+    par_n = rel(hCn, Cn_dev)
+    par_t = rel(hCt[:, :Ct_dev.shape[1]], Ct_dev)       # rank 0's SNP rows come first
+
+    # pageable panels: plain numpy arrays, as a Julia Matrix{Float64} / Fortran array would be
+    pBn, pBt = hBn.numpy().copy(), hBt.numpy().copy()
+    pCn, pCt = np.empty((ncol, indiv)), np.empty((ncol, snps))
+
+    def step_pageable():
+        call(b"N", pBn.ctypes.data, snps, pCn.ctypes.data, indiv)
+        call(b"T", pBt.ctypes.data, indiv, pCt.ctypes.data, snps)
+    pmean_s, pbest_s = _wall_steps(step_pageable, steps, 2)
+    par_p = max(rel(torch.from_numpy(pCn), hCn), rel(torch.from_numpy(pCt), hCt))
+    if own:
+        lib.free_compressed(C.byref(handle))
+    units = 2.0 * snps * indiv * ncol
+    nbytes = 8 * ncol * (snps + indiv)
+    return {"value": units / mean_s, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+            "d2h_bytes_per_step": nbytes, "steps": steps, "ms_per_step": mean_s * 1e3,
+            "best_ms_per_step": best_s * 1e3, "n_ms": n_s * 1e3, "t_ms": t_s * 1e3,
+            "timing": "wall clock around the blocking calls, mean of %d steps after 2 warm-ups" % steps,
+            "api": ("dgemm_compressed() C-ABI, pinned host B/C" if nsh == 1 else
+                    "dgemm_compressed() C-ABI on ONE sharded handle: one process, %d device shards %s, "
+                    "peer-memory all-gather ('t') / reduce-scatter ('n'), pinned host B/C" % (nsh, devices)),
+            "devices": devices, "shards": nsh, "gpu_launches_per_step": int(launches),
+            "pageable": {"value": units / pmean_s, "ms_per_step": pmean_s * 1e3,
+                         "best_ms_per_step": pbest_s * 1e3, "vs_pinned": pmean_s / mean_s,
+                         "what": "the same calls with pageable numpy panels (staged through the "
+                                 "library's pinned ring)"},
+            "parity": {"n_vs_device_arm": par_n, "t_vs_device_arm": par_t, "pageable_vs_pinned": par_p,
+                       "ok": bool(par_n <= 1e-10 and par_t <= 1e-10 and par_p <= 1e-10),
+                       "bar": "max|dC|/max|C| <= 1e-10"}}
+
+
+def run_small(lib, api):
+    """BASELINE configs[0]: dgemm_compressed 'n', ncol = 1, 10k SNPs x 1k individuals -- the
+    reference's own test case (tests/dgemm_compressed); latency of the C-ABI call with pageable
+    host vectors.  Reported, not a roofline case (the matrix is 2.5 MB)."""
+    import numpy as np
+    snps, indiv = 10_000, 1_000
+    h = api.simulate_compressed(snps, indiv, 5, 1)
+    rng = np.random.default_rng(1)
+    B = rng.standard_normal(snps)
+    Cout = np.empty(indiv)
+    ts = []
+    for it in range(120):
+        t0 = time.perf_counter()
+        lib.dgemm_compressed(b"N", h, 1, B.ctypes.data, snps, Cout.ctypes.data, indiv)
+        if it >= 20:
+            ts.append(time.perf_counter() - t0)
+    ok = lib.mb200_last_status() == 0
+    lib.free_compressed(C.byref(h))
+    return {"workload": "dgemm_compressed 'n', ncol=1, 10000 SNPs x 1000 individuals (BASELINE configs[0])",
+            "ms_median": statistics.median(ts) * 1e3, "ms_best": min(ts) * 1e3, "calls": len(ts),
+            "value": snps * indiv / statistics.median(ts), "unit": UNIT, "ok": ok,
+            "api": "dgemm_compressed() C-ABI, pageable host vectors, wall clock per call"}
+
+
+def run_pcg(args, lib, api, dev, rank, world, host_barrier=lambda: None, e2e_devices=None):
     """BASELINE configs[3]: conjugate gradients on (Zc Zc^T + lambda I) x = b, 500k SNPs x 200k
     individuals, packed matrix resident and SNP-sharded over the ranks; one iteration = one 't' and
     one 'n' product with a single column + ONE all-reduce of indiv doubles (mb200_cg_solve_device).
@@ -417,8 +545,8 @@ def run_pcg(args, lib, api, dev, rank, world):
     sh = ShardedCompressed(None, snps, indiv, rank, world)
     s_loc, bs = sh.s_count, (indiv + 3) // 4
     bed = torch.empty(s_loc * bs, dtype=torch.uint8, device=dev)
-    api._check(lib.mb200_simulate_plink_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, 3000 + rank),
-               "simulate")
+    api._check(lib.mb200_simulate_plink_rows_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, 3000,
+                                                    sh.s_begin), "simulate")
     h = C.c_void_p(None)
     api._check(lib.mb200_plink2compressed_device(C.c_void_p(bed.data_ptr()), s_loc, indiv, None, 1,
                                                  C.byref(h)), "plink2compressed_device")
@@ -426,9 +554,9 @@ def run_pcg(args, lib, api, dev, rank, world):
     torch.cuda.empty_cache()
     sh.handle = h
     stream = sh.stream()
-    g = torch.Generator(device=dev)
-    g.manual_seed(11)
-    b = torch.randn(indiv, dtype=torch.float64, device=dev, generator=g)
+    import numpy as np
+    hb = np.random.default_rng(11).standard_normal(indiv)
+    b = torch.from_numpy(hb).to(dev)
     x = torch.zeros(indiv, dtype=torch.float64, device=dev)
     lam = 0.05 * snps
     sh.cg_solve(b, x, lam=lam, tol=0.0, max_iter=2)  # warm-up (workspace, NCCL channel)
@@ -447,6 +575,34 @@ def run_pcg(args, lib, api, dev, rank, world):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     launches = api.kernel_launches() - launches0
     bnorm = float(b.norm().item())
+    x_dev = x.cpu().numpy()
+    # e2e: mb200_cg_solve with HOST vectors, one process; at N > 1 rank 0 alone on a sharded handle
+    torch.cuda.synchronize()
+    host_barrier()
+    e2e = None
+    if rank == 0:
+        devices = e2e_devices or list(range(world))
+        own = len(devices) > 1
+        hh = h
+        if own:
+            api.set_devices(devices)
+            try:
+                hh = api.simulate_compressed(snps, indiv, 3000, 1)
+            finally:
+                api.set_devices(None)
+        api.cg_solve(hh, hb, np.zeros(indiv), lam=lam, tol=0.0, max_iter=2)
+        t0 = time.perf_counter()
+        xe, ite, rese = api.cg_solve(hh, hb, np.zeros(indiv), lam=lam, tol=0.0, max_iter=iters)
+        sec = time.perf_counter() - t0
+        if own:
+            lib.free_compressed(C.byref(hh))
+        e2e = {"ms_per_iteration": sec * 1e3 / (ite + 1), "iterations": ite,
+               "value": 2.0 * snps * indiv / (sec / (ite + 1)), "unit": UNIT, "devices": devices,
+               "api": "mb200_cg_solve() C-ABI, host vectors, one process"
+                      + (", sharded handle over %d devices" % len(devices) if own else ""),
+               "x_vs_device_arm": float(np.abs(xe - x_dev).max() / max(np.abs(x_dev).max(), 1e-300)),
+               "residual_reduction": rese / bnorm}
+    host_barrier()
     sh._stream = None
     del stream
     lib.free_compressed(C.byref(h))
@@ -461,14 +617,119 @@ def run_pcg(args, lib, api, dev, rank, world):
                         f"(BASELINE configs[3]), packed matrix resident, SNP-sharded over {world} GPU(s)",
             "iterations": it, "ms_per_iteration": ms_iter,
             "value": 2.0 * snps * indiv / (ms_iter * 1e-3), "unit": UNIT,
-            "residual_reduction": res / bnorm, "gpu_launches": int(launches),
+            "residual_reduction": res / bnorm, "gpu_launches": int(launches), "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU",
                          "frac": gbs / hbm,
                          "note": "algorithmic bytes = both packed orientations once per iteration "
                                  "(ncol = 1: 't' then 'n'), per GPU"}}
 
 
-def run_grm_partition(args, lib, api, dev, rank, world, snps, indiv, label, reps=None, warm=None):
+
+def int8_peak_file():
+    """(peak TOP/s, source).  profiles/int8_peak.json holds the cuBLASLt int8 rate MEASURED on this
+    pool (written from an earlier bench run); the nominal dense figure is the fallback."""
+    f = os.path.join(ROOT, "profiles", "int8_peak.json")
+    try:
+        d = json.load(open(f))
+        return float(d["nominal_dense_tops"]), float(d["measured_cublaslt_tops"]), "profiles/int8_peak.json"
+    except Exception:
+        return 4500.0, None, "nominal int8 dense (no profiles/int8_peak.json)"
+
+
+def _mem_available_bytes():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) * 1024
+    except Exception:
+        pass
+    return 0
+
+
+def grm_row_sums_exact(lib, api, h, snps, indiv):
+    """m = Z (Z^T 1) and its total, exactly, through dgemm_compressed itself (not centred, 8 digits:
+    integer-exact), for the sampled parity check of the GRM legs."""
+    import numpy as np
+    api.set_options(use_gpu=True, not_center=True)
+    try:
+        colsum = api.dgemm_compressed("T", h, np.ones((indiv, 1), order="F"), snps, indiv)
+        m = api.dgemm_compressed("N", h, colsum, snps, indiv).ravel()
+    finally:
+        api.set_options(use_gpu=True, not_center=False)
+    return m, float(m.sum())
+
+
+def grm_sampled_parity(G, hx, indiv, m, total, c, samples=32, seed=3):
+    """Sampled entries (both triangles) of a centred+scaled GRM against direct int64 dot products of
+    the decoded packed rows and the update of crossproduct.jl:91-106 in numpy long double."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    n = indiv
+    ii = rng.integers(0, n, samples)
+    jj = rng.integers(0, n, samples)
+    ii[0], jj[0] = 0, n - 1
+    ii[1], jj[1] = n - 1, n - 1
+    ii[2] = jj[2]                                  # a diagonal entry
+    shifts = np.arange(4, dtype=np.uint8) * 2
+
+    def row(i):
+        b = np.asarray(hx[i])
+        return ((b[:, None] >> shifts[None, :]) & 3).reshape(-1).astype(np.int64)
+    worst, gmax = 0.0, float(np.abs(G[ii, jj]).max())
+    for i, j in zip(ii.tolist(), jj.tolist()):
+        cnt = int(row(i) @ row(j))
+        want = (np.longdouble(cnt) - (np.longdouble(m[i]) + np.longdouble(m[j])) / n
+                + np.longdouble(total) / n / n) / np.longdouble(c)
+        for got in (G[i, j], G[j, i]):
+            worst = max(worst, abs(float(got - want)))
+    gmax = max(gmax, 1e-300)
+    return {"samples": int(samples), "max_abs_err": worst, "max_abs_value": gmax,
+            "rel": worst / gmax, "ok": bool(worst <= 1e-10 * gmax),
+            "bar": "|dG| <= 1e-10 max|G| on sampled (i,j) and (j,i) against int64 dot products"}
+
+
+def grm_e2e(lib, api, hx, kcols, indiv, hf, devices, pinned, reps, parity=None):
+    """mb200_grm() host call (= snp_multiply_gpu + the fused crossproduct.jl:83-110 epilogue) over
+    `devices`, one process: packed matrix and fp64 result in HOST memory, both PCIe legs and all
+    device allocations inside the timed region (wall clock; the call blocks)."""
+    import numpy as np
+    import torch
+    need = 8 * indiv * indiv
+    if need * 1.15 > _mem_available_bytes():
+        return {"skipped": "host memory: result needs %.1f GB, %.1f GB available"
+                           % (need / 1e9, _mem_available_bytes() / 1e9)}, None
+    if pinned:
+        hans_t = torch.empty(indiv * indiv, dtype=torch.float64).pin_memory()
+        hans = hans_t.numpy().reshape(indiv, indiv)
+    else:
+        hans = np.empty((indiv, indiv))
+        hans.fill(0.0)                                   # first touch outside the timed region
+    api.set_devices(devices if len(devices) > 1 else None)
+    ts = []
+    try:
+        for it in range(reps + 1):
+            t0 = time.perf_counter()
+            api._check(lib.mb200_grm(C.c_void_p(hx.ctypes.data), kcols, indiv, C.c_void_p(hans.ctypes.data),
+                                     False, C.c_void_p(hf.ctypes.data), True), "mb200_grm")
+            if it >= 1 or reps == 0:
+                ts.append(time.perf_counter() - t0)
+    finally:
+        api.set_devices(None)
+    t = api.crossprod_last_timing()
+    out = {"ms": statistics.mean(ts) * 1e3, "best_ms": min(ts) * 1e3, "device_pipeline_ms": t["gemm_ms"],
+           "h2d_bytes_per_step": int(hx.nbytes + 8 * kcols), "d2h_bytes_per_step": int(need),
+           "devices": devices, "host_memory": "pinned" if pinned else "pageable",
+           "api": "mb200_grm() C-ABI host call, one process, %d device(s), %d timed call(s) after 1 warm-up"
+                  % (len(devices), len(ts))}
+    if parity is not None:
+        m, total, c = parity
+        out["sampled_parity"] = grm_sampled_parity(hans, hx, indiv, m, total, c)
+    out["symmetric"] = bool(np.array_equal(hans[:257, :4096], hans[:4096, :257].T))
+    return out, hans
+
+
+def run_grm_partition(args, lib, api, dev, rank, world, snps, indiv, label, reps=None, warm=None,
+                      host_barrier=lambda: None, e2e_devices=None, sampled=False):
     """configs[1]/[4] over N GPUs: 2-D output-tile partition, NO communication -- every rank holds
     the packed matrix and computes the 128-row tiles t with t % N == rank of the centred GRM
     (mb200_crossprod_partition_device).  Time = max over ranks of the device time."""
@@ -504,28 +765,63 @@ def run_grm_partition(args, lib, api, dev, rank, world, snps, indiv, label, reps
             epi.append(t["epilogue_ms"])
             ops = t["executed_ops"]
     torch.cuda.synchronize()
+    # e2e leg (rank 0, one process over all GPUs): the packed matrix goes to HOST memory first
+    e2e_in = None
+    if rank == 0:
+        import numpy as np
+        nbytes = indiv * lay.pitch_indiv_major
+        hx = np.empty((indiv, lay.pitch_indiv_major), dtype=np.uint8)
+        step = max(1, (1 << 30) // lay.pitch_indiv_major)
+        for r0 in range(0, indiv, step):                      # 1 GiB pieces through torch's D2H
+            r1 = min(indiv, r0 + step)
+            hx[r0:r1] = _device_bytes(lay.d_indiv_major + r0 * lay.pitch_indiv_major,
+                                      (r1 - r0) * lay.pitch_indiv_major, dev).cpu().numpy().reshape(r1 - r0, -1)
+        hf = f.cpu().numpy()
+        par = None
+        if sampled:
+            m_exact, total = grm_row_sums_exact(lib, api, h, snps, indiv)
+            par = (m_exact, total, float(2.0 * (hf * (1.0 - hf)).sum()))
+        e2e_in = (hx, hf, par)
     lib.free_compressed(C.byref(h))
-    del panel
+    del panel, f
     torch.cuda.empty_cache()
     v = torch.tensor([statistics.mean(gemm), statistics.mean(epi), ops], dtype=torch.float64, device=dev)
     vmax = v.clone()
     dist.all_reduce(vmax, op=dist.ReduceOp.MAX)
     dist.all_reduce(v, op=dist.ReduceOp.SUM)
+    torch.cuda.synchronize()
+    host_barrier()
+    e2e = None
+    if rank == 0:
+        hx, hf, par = e2e_in
+        devices = e2e_devices or list(range(world))
+        big = indiv * indiv * 8 > 8e9
+        try:
+            e2e, _hans = grm_e2e(lib, api, hx, kcols, indiv, hf, devices, pinned=not big,
+                                 reps=1 if big else 3, parity=par)
+            del _hans
+        except Exception as exc:  # the leg is reported, never fatal for the headline
+            e2e = {"error": repr(exc)}
+        if isinstance(e2e, dict) and "ms" in e2e:
+            e2e["value"] = 2.0 * indiv * indiv * snps / (e2e["ms"] * 1e-3) / 1e12
+            e2e["unit"] = "TOPS"
+        del hx
+    host_barrier()
     if rank != 0:
         return None
     gm, ep, ops_sum = float(vmax[0]), float(vmax[1]), float(v[2])
     tot = gm + ep
     alg_ops = 2.0 * indiv * indiv * snps
-    int8_peak = 4500.0
-    return {"workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals ({label}), "
+    int8_peak_v, int8_meas, int8_src = int8_peak_file()
+    return {"e2e": e2e, "workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals ({label}), "
                         f"2-D output-tile partition over {world} GPUs, no communication",
             "metric": "GRM crossproduct int8 TOPS", "value": alg_ops / (tot * 1e-3) / 1e12,
             "unit": "TOPS (2*indiv^2*snps / t, full-matrix count)", "ms": tot,
             "expand_gemm_ms": gm, "epilogue_ms": ep,
             "roofline": {"bound": "tensor", "achieved": ops_sum / (gm * 1e-3) / 1e12 / world,
-                         "peak": int8_peak, "unit": "TOP/s per GPU",
-                         "frac": ops_sum / (gm * 1e-3) / 1e12 / world / int8_peak, "traffic": None,
-                         "peak_source": "nominal int8 dense",
+                         "peak": int8_peak_v, "unit": "TOP/s per GPU",
+                         "frac": ops_sum / (gm * 1e-3) / 1e12 / world / int8_peak_v, "traffic": None,
+                         "peak_source": int8_src, "peak_measured_library": int8_meas,
                          "note": "achieved = EXECUTED ops of all ranks / (max expand+GEMM time x N)"}}
 
 
@@ -614,36 +910,31 @@ def run_grm(args, lib, api, dev):
             ops = t["executed_ops"]
     torch.cuda.synchronize()
     # end to end through the reference-facing host call (mb200_grm = snp_multiply_gpu + the fused
-    # crossproduct.jl:83-110 epilogue): packed matrix and fp64 result in pinned HOST memory, both
-    # PCIe copies and the device allocations inside the timed region (wall clock, the call blocks).
+    # crossproduct.jl:83-110 epilogue): packed matrix and fp64 result in HOST memory (pinned, then
+    # pageable), both PCIe legs and the device allocations inside the timed region.
     e2e = None
     try:
+        import numpy as np
         nbytes = indiv * lay.pitch_indiv_major
-        hx = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-        hx.copy_(_device_bytes(lay.d_indiv_major, nbytes, dev))
-        hf = f.cpu().pin_memory()
-        hans = torch.empty(indiv * indiv, dtype=torch.float64, pin_memory=True)
-        ts = []
-        for it in range(4):
-            t0 = time.perf_counter()
-            api._check(lib.mb200_grm(C.c_void_p(hx.data_ptr()), kcols, indiv, C.c_void_p(hans.data_ptr()),
-                                     False, C.c_void_p(hf.data_ptr()), True), "mb200_grm")
-            if it >= 1:
-                ts.append(time.perf_counter() - t0)
-        same = bool(torch.equal(hans, ans.cpu()))
-        e2e = {"value": 2.0 * indiv * indiv * snps / statistics.mean(ts) / 1e12, "unit": "TOPS",
-               "ms": statistics.mean(ts) * 1e3, "best_ms": min(ts) * 1e3,
-               "h2d_bytes_per_step": nbytes + 8 * kcols, "d2h_bytes_per_step": 8 * indiv * indiv,
-               "api": "mb200_grm() host call, pinned host buffers, 3 calls after 1 warm-up",
-               "matches_device_result": same}
+        hx = _device_bytes(lay.d_indiv_major, nbytes, dev).cpu().numpy().reshape(indiv, -1)
+        hf = f.cpu().numpy()
+        m_exact, total = grm_row_sums_exact(lib, api, h, snps, indiv)
+        par = (m_exact, total, float(2.0 * (hf * (1.0 - hf)).sum()))
+        e2e, hans = grm_e2e(lib, api, hx, kcols, indiv, hf, [0], pinned=True, reps=3, parity=par)
+        e2e["value"] = 2.0 * indiv * indiv * snps / (e2e["ms"] * 1e-3) / 1e12
+        e2e["unit"] = "TOPS"
+        e2e["matches_device_result"] = bool(np.array_equal(hans, ans.cpu().numpy().reshape(indiv, indiv)))
+        del hans
+        pg, hans = grm_e2e(lib, api, hx, kcols, indiv, hf, [0], pinned=False, reps=3)
+        e2e["pageable"] = {"ms": pg["ms"], "best_ms": pg["best_ms"], "vs_pinned": pg["ms"] / e2e["ms"]}
         del hx, hans
-    except Exception as e:  # the leg is reported, never fatal for the headline
-        e2e = {"error": repr(e)}
+    except Exception as exc:  # the leg is reported, never fatal for the headline
+        e2e = {"error": repr(exc)}
     lib.free_compressed(C.byref(h))
     alg_ops = 2.0 * indiv * indiv * snps
     gm = statistics.mean(gemm)
     tot = gm + statistics.mean(epi)
-    int8_peak = 4500.0  # nominal dense int8 TOPS per B200 (no int8 entry in MEASURED_PEAKS.json)
+    int8_peak, _int8_meas, int8_src = int8_peak_file()
     lib_int8 = library_int8_peak(dev, indiv, snps)
     return {"library_int8": lib_int8, "e2e": e2e,
             "workload": f"centred+scaled GRM, {snps} SNPs x {indiv} individuals (BASELINE configs[1])",
@@ -652,7 +943,7 @@ def run_grm(args, lib, api, dev):
             "expand_gemm_ms": gm, "epilogue_ms": statistics.mean(epi),
             "roofline": {"bound": "tensor", "achieved": ops / (gm * 1e-3) / 1e12, "peak": int8_peak,
                          "unit": "TOP/s", "frac": ops / (gm * 1e-3) / 1e12 / int8_peak,
-                         "traffic": _grm_traffic(snps, indiv), "peak_source": "nominal int8 dense",
+                         "traffic": _grm_traffic(snps, indiv), "peak_source": int8_src,
                          "peak_measured_library": (lib_int8.get("square_8192") or {}).get("best_tops"),
                          "note": "achieved = EXECUTED ops (upper-triangle tiles only) / expand+GEMM time; "
                                  "peak_measured_library = cuBLASLt int8 8192^3 on this box"}}
@@ -669,6 +960,30 @@ def run_cpu_baseline(args):
             "sample": f"{snps} SNPs x {indiv} individuals sub-block, ncol={args.ncol}, 'N'+'T' per step, "
                       f"3 steps after 1 warm-up, reference CPU 5codes variant 256, {cores} threads; "
                       f"{sec:.2f} s/step"}
+
+
+def run_small_cpu_baseline():
+    """configs[0] on the reference CPU 5codes library: 'N', ncol = 1, 10k SNPs x 1k individuals."""
+    import numpy as np
+    from oracle import ref, simulate
+    snps, indiv = 10_000, 1_000
+    cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    plink, _, f = simulate.simulate(snps, indiv, seed=5)
+    ref.set_options(cores=cores, centered=True, variant=256)
+    h = ref.RefCompressed(plink, snps, indiv, f, 1)
+    B = np.asfortranarray(np.random.default_rng(1).standard_normal((snps, 1)))
+    Cout = np.zeros((indiv, 1), order="F")
+    ts = []
+    for it in range(40):
+        t0 = time.perf_counter()
+        h.dgemm("N", B, Cout)
+        if it >= 5:
+            ts.append(time.perf_counter() - t0)
+    h.free()
+    return {"ms_median": statistics.median(ts) * 1e3, "ms_best": min(ts) * 1e3, "cores": cores,
+            "value": snps * indiv / statistics.median(ts), "unit": UNIT, "kind": "reference",
+            "sample": f"the whole of configs[0], 35 calls after 5 warm-ups, reference CPU 5codes variant 256, {cores} threads"}
 
 
 def run_grm_cpu_baseline(snps=16_000, indiv=2_000):

@@ -212,6 +212,9 @@ int mb200_download_layout(void *compressed, unsigned char *snp_major, unsigned c
  * d_plink: snps x ceil(indiv/4) bytes on the current device. */
 int mb200_simulate_plink_device(unsigned char *d_plink, long snps, long indiv,
                                 unsigned long long seed);
+/* SNP rows [snp_offset, snp_offset + snps) of the matrix with that seed (a shard of it). */
+int mb200_simulate_plink_rows_device(unsigned char *d_plink, long snps, long indiv,
+                                     unsigned long long seed, long snp_offset);
 
 /* Crossproduct on device-resident input.  d_x: rows x ceil(k/4) bytes.  d_counts (optional,
  * may be NULL): rows x rows int32 row-major upper-triangle-valid scratch is internal; d_ans:

@@ -58,6 +58,7 @@ SIGNATURES = {
     "mb200_get_layout": (C.c_int, [C.c_void_p, C.POINTER(Layout)]),
     "mb200_download_layout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mb200_simulate_plink_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_ulonglong]),
+    "mb200_simulate_plink_rows_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_ulonglong, C.c_long]),
     "mb200_crossprod_device": (C.c_int, [C.c_void_p, C.c_long, C.c_long, C.c_int, C.c_int,
                                          C.c_void_p, C.c_int, C.c_void_p]),
     "mb200_grm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_bool, C.c_void_p, C.c_bool]),

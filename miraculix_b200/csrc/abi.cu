@@ -679,6 +679,14 @@ int mb200_simulate_plink_device(unsigned char *d_plink, long snps, long indiv,
   return 0;
 }
 
+int mb200_simulate_plink_rows_device(unsigned char *d_plink, long snps, long indiv,
+                                     unsigned long long seed, long snp_offset) {
+  clear_status();
+  MB_CHECK(simulate_plink(d_plink, snps, indiv, seed, 0, snp_offset));
+  MB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
 int mb200_crossprod_device(const unsigned char *d_x, long k, long rows, int is_plink_format,
                            int mode, const double *d_f, int do_scale, double *d_ans) {
   clear_status();
@@ -747,7 +755,7 @@ static int crossprod_host(const unsigned char *x, int k, int rows, double *ans, 
     return fail(-2, __func__, __LINE__, "bad arguments (k=%d rows=%d)", k, rows) ? 1 : 1;
   std::vector<int> devs;
   if (multi_device_list(&devs)) return 1;
-  if (mode != 2) {
+  if (mode != 2 && options().crossprod_mode >= 1) {  // (the SIMT cross-check family stays in core)
     const int rc = crossprod_host_tiled(x, k, rows, ans, is_plink, mode, f, do_scale, devs, &t_cp_timing);
     if (!rc && print_level() >= 0)
       printf("miraculix_b200: crossproduct %d x %d on %d device(s): device pipeline %.2f ms\n", rows, k,
@@ -772,9 +780,10 @@ static int crossprod_host(const unsigned char *x, int k, int rows, double *ans, 
   X_CUDA(pool_alloc(&d_x, (size_t)rows * nb, st));
   X_CUDA(pool_alloc(&d_ans, sizeof(double) * rows * rows, st));
   X_CUDA(cudaMemcpyAsync(d_x, x, (size_t)rows * nb, cudaMemcpyHostToDevice, st));
-  if (f) {
-    X_CUDA(pool_alloc(&d_f, sizeof(double) * rows, st));
-    X_CUDA(cudaMemcpyAsync(d_f, f, sizeof(double) * rows, cudaMemcpyHostToDevice, st));
+  if (f && mode) {
+    const long nf = mode == 1 ? k : rows;
+    X_CUDA(pool_alloc(&d_f, sizeof(double) * nf, st));
+    X_CUDA(cudaMemcpyAsync(d_f, f, sizeof(double) * nf, cudaMemcpyHostToDevice, st));
   }
   if (!rc) rc = crossprod_device(d_x, k, rows, is_plink, mode, d_f, do_scale, d_ans, st, &t_cp_timing);
   X_CUDA(cudaMemcpyAsync(ans, d_ans, sizeof(double) * rows * rows, cudaMemcpyDeviceToHost, st));

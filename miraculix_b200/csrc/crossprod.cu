@@ -356,22 +356,24 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
 
 // ---------------------------------------------------------------------------------------------
 // Building blocks of the out-of-core / multi-device host path (crossprod_host.cu): the int32
-// counts of one partition's row tiles over all K slabs (no fp64 epilogue: the finishing kernel
-// there converts chunk by chunk while earlier chunks are on their way to the host), and the GRM
-// row sums.  C32: [round_up(local_rows, 256)][round_up(rows, 256)] int32; the entries of local
-// row lr (global row i) are valid from column 256 floor(i / 256) on.
+// counts of a BAND of consecutive row tiles [tile_begin, tile_end) over all K slabs (no fp64
+// epilogue: the finishing kernel there converts chunk by chunk while earlier chunks are on their
+// way to the host), and the GRM row sums.  C32: [round_up(band rows, 256)][round_up(rows, 256)]
+// int32; local row lr is global row 128 tile_begin + lr, valid from column 256 floor(i / 256) on.
 // ---------------------------------------------------------------------------------------------
-int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int part,
-                               int nparts, int32_t *C32, cudaStream_t stream, double *executed_ops) {
+int build_band_tile_list(long rows, int tile_begin, int tile_end, TileCoord **d_tiles, int *num_tiles,
+                         cudaStream_t stream, int *real_tiles, int pair);
+
+int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int tile_begin,
+                          int tile_end, int32_t *C32, cudaStream_t stream, double *executed_ops) {
   if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
-  if (nparts < 1 || part < 0 || part >= nparts)
-    return fail(-2, __func__, __LINE__, "bad partition %d of %d", part, nparts);
+  if (tile_begin < 0 || tile_end <= tile_begin || (tile_begin & 1))
+    return fail(-2, __func__, __LINE__, "bad band [%d, %d)", tile_begin, tile_end);
   int device = 0;
   MB_CUDA(cudaGetDevice(&device));
   const int sms = device_sm_count(device);
   const long nb = ceil_div(k, 4);
   const long rows_pad = round_up(rows, 256);
-  if (crossprod_partition_rows(rows, part, nparts) == 0) return 0;
   double slab_gb = 8.0;
   if (const char *e = getenv("MB200_SLAB_GB")) slab_gb = atof(e) > 0 ? atof(e) : slab_gb;
   long slab_kbytes = (long)(slab_gb * 1073741824.0 / (double)rows_pad) / 4 / 32 * 32;
@@ -381,12 +383,11 @@ int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_pli
   if (is_plink_format) MB_CHECK(upload_lut());
   int8_t *X8 = nullptr;
   TileCoord *d_tiles = nullptr;
-  int num_tiles = 0, real_tiles = 0, num_tail = 0;
+  int num_tiles = 0, real_tiles = 0;
   CallScratch scratch(stream);
   MB_CUDA(scratch.alloc(&X8, (size_t)rows_pad * kpad));
-  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? nparts : 0;
-  MB_CHECK(build_tile_list(rows, part, nparts, &d_tiles, &num_tiles, stream, 0,
-                           crossprod_tc_units(sms, pair), &num_tail, &real_tiles, pair));
+  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? 1 : 0;
+  MB_CHECK(build_band_tile_list(rows, tile_begin, tile_end, &d_tiles, &num_tiles, stream, &real_tiles, pair));
   scratch.adopt(d_tiles);
   int slab = 0;
   for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
@@ -395,9 +396,13 @@ int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_pli
     expand_2bit_launch(d_x, rows, nb, kb0, kbytes, is_plink_format, X8, rows_pad, kpad, sms, stream);
     count_launch();
     MB_LAUNCH_CHECK();
-    MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
-                                 sms, stream, nullptr, 0, pair));
-    if (executed_ops) *executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
+    if (options().crossprod_mode >= 1) {
+      MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
+                                   sms, stream, nullptr, 0, pair));
+      if (executed_ops) *executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
+    } else {
+      return fail(-2, __func__, __LINE__, "the tiled host path needs the tensor-core crossproduct (mode 1 or 2)");
+    }
   }
   return 0;  // `scratch` frees stream-ordered: the slab outlives the kernels enqueued above
 }

@@ -7,14 +7,15 @@
 // Device g of N (one host thread each, team.h):
 //   1. uploads 1/N of the packed matrix and pulls the rest from the peers (NVLink), so the input
 //      crosses PCIe once in total;
-//   2. for every pass t: accumulates the int32 counts of partition g + N t of N * passes (cyclic
-//      128-row tiles: balanced over the upper triangle, crossprod.cu) over all K slabs;
-//   3. finish_chunk_kernel turns a chunk of row tiles into fp64 -- with the exact GRM update of
-//      crossproduct.jl:91-106 -- in BOTH orientations, and the chunk streams into the caller's
-//      column-major matrix as it is: rows of the panel are columns of `ans` below the diagonal,
-//      the transposed copy fills the part above it (the reference's ans[j,i] = ans[i,j] scatter).
-//      Chunks are double-buffered: the copy of one overlaps the finishing of the next and the
-//      GEMM of the next pass.
+//   2. for every band it owns: accumulates the int32 counts of a band of consecutive row tiles
+//      (against all column tiles at or right of the diagonal) over all K slabs; bands have about
+//      equal AREA of the upper triangle and are dealt round-robin, so the devices stay balanced;
+//   3. finish_chunk_kernel turns a chunk of the band's rows into fp64 -- with the exact GRM update
+//      of crossproduct.jl:91-106 -- in BOTH orientations, and the chunk streams into the caller's
+//      column-major matrix with two large 2-D copies: the rows of the panel are the columns of
+//      `ans` from the chunk's first row down, the transposed panel fills the same columns' rows
+//      to the right (the reference's ans[j,i] = ans[i,j] scatter).  Chunks are double-buffered:
+//      the copy of one overlaps the finishing of the next and the GEMM of the next band.
 // Pageable `ans` / `x` (Julia, Fortran arrays) go through the pinned ring of stager.h.
 #include <stdlib.h>
 #include <string.h>
@@ -27,36 +28,57 @@ namespace mb200 {
 
 constexpr int FC_T = 32;  // 32 x 32 sub-tiles
 
-// counts C32[lr][j] (ld32) of local rows [lr0, lr0 + crows) -> P[lr - lr0][j] (row-major, ld n) and
-// PT[j][lr - lr0] (ld crows).  Global row of local row lr: ((lr / 128) nparts + part) 128 + lr % 128.
-// Only columns from the row tile's first computed column tile on are produced.
+// Chunk = global rows [c0, c0 + crows) (c0 a multiple of 256) of the band that starts at global
+// row b0; counts C32[i - b0][j] (ld32) are valid for j >= 256 floor(i / 256).  For every i of the
+// chunk and every column j >= c0:   P[i - c0][j - c0] (ld n - c0)  and  PT[j - c0][i - c0] (ld crows)
+// receive the finished value; entries left of a row's diagonal tile (c0 <= j < 256 floor(i / 256))
+// are taken from the mirrored count C32[j - b0][i], which lies in the same chunk.
 __global__ void __launch_bounds__(256)
-finish_chunk_kernel(const int32_t *__restrict__ C32, long ld32, long lr0, long crows, long n,
-                    int part, int nparts, int affine, int do_scale, const double *__restrict__ m,
+finish_chunk_kernel(const int32_t *__restrict__ C32, long ld32, long b0, long c0, long crows, long n,
+                    int affine, int do_scale, const double *__restrict__ m,
                     const double *__restrict__ scal, double *__restrict__ P, double *__restrict__ PT) {
   __shared__ double t[FC_T][FC_T + 1];
-  const long rb = (long)blockIdx.y * FC_T;          // row offset inside the chunk
-  const long lt = (lr0 + rb) / 128;                 // local row tile
-  const long gi0 = (lt * nparts + part) * 128 + (lr0 + rb) % 128;  // global row of sub-tile row 0
-  const long first = ((lt * nparts + part) & ~1L) * 128;
-  const long j0 = (long)blockIdx.x * FC_T;
-  if (j0 + FC_T <= first || gi0 >= n) return;       // left of the diagonal tile / row padding
+  const long i0 = c0 + (long)blockIdx.y * FC_T;   // global row of sub-tile row 0
+  const long j0 = c0 + (long)blockIdx.x * FC_T;   // global column of sub-tile column 0
+  if (i0 >= n || j0 >= n) return;
+  const long first = i0 / 256 * 256;              // same for the 32 rows of the sub-tile
+  const bool mirrored = j0 < first;               // whole sub-tile left of the diagonal tile
   const CpAffine aff = cp_affine_setup(n, affine, do_scale, scal);
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  for (int yy = ty; yy < FC_T; yy += 8) {
-    const long gi = gi0 + yy, j = j0 + tx;
-    double v = 0.0;
-    if (gi < n && j < n && j >= first) {
-      const int cnt = C32[(lr0 + rb + yy) * ld32 + j];
-      v = affine ? cp_affine_m(cnt, m[gi], m[j], aff) : (double)cnt;
-      P[(rb + yy) * n + j] = v;
+  const long w = n - c0;
+  if (!mirrored) {
+    for (int yy = ty; yy < FC_T; yy += 8) {
+      const long i = i0 + yy, j = j0 + tx;
+      double v = 0.0;
+      if (i < n && j < n) {
+        const int cnt = C32[(i - b0) * ld32 + j];
+        v = affine ? cp_affine_m(cnt, m[i], m[j], aff) : (double)cnt;
+        P[(i - c0) * w + (j - c0)] = v;
+      }
+      t[yy][tx] = v;
     }
-    t[yy][tx] = v;
-  }
-  __syncthreads();
-  for (int yy = ty; yy < FC_T; yy += 8) {
-    const long j = j0 + yy, gi = gi0 + tx;
-    if (gi < n && j < n && j >= first) PT[j * crows + rb + tx] = t[tx][yy];
+    __syncthreads();
+    for (int yy = ty; yy < FC_T; yy += 8) {
+      const long j = j0 + yy, i = i0 + tx;
+      if (i < n && j < n) PT[(j - c0) * crows + (i - c0)] = t[tx][yy];
+    }
+  } else {
+    // value (i, j) = value (j, i): read C32 rows j (coalesced along i), write PT directly, P via smem
+    for (int yy = ty; yy < FC_T; yy += 8) {
+      const long j = j0 + yy, i = i0 + tx;
+      double v = 0.0;
+      if (i < n && j < n) {
+        const int cnt = C32[(j - b0) * ld32 + i];
+        v = affine ? cp_affine_m(cnt, m[j], m[i], aff) : (double)cnt;
+        PT[(j - c0) * crows + (i - c0)] = v;
+      }
+      t[yy][tx] = v;
+    }
+    __syncthreads();
+    for (int yy = ty; yy < FC_T; yy += 8) {
+      const long i = i0 + yy, j = j0 + tx;
+      if (i < n && j < n) P[(i - c0) * w + (j - c0)] = t[tx][yy];
+    }
   }
 }
 
@@ -130,37 +152,54 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
   const int N = (int)devs.size();
   const long nb = ceil_div(k, 4), rows_pad = round_up(rows, 256);
 
-  // Passes: the int32 accumulator of one pass holds ceil(Mt / (N passes)) row tiles.  TILE_SIZE
-  // (the reference's knob, rows here) and MB200_GRM_ACC_GB (default 16 GiB) bound it; a few passes
-  // are used even when one would fit, so that the download of one overlaps the GEMM of the next.
+  // Bands of consecutive row tiles (even tile counts: CTA pairs, 256-row diagonal blocks).  Their
+  // height is capped by TILE_SIZE (the reference's knob, rows here) and MB200_GRM_ACC_GB (bytes of
+  // the int32 accumulator, default 16 GiB); within the cap they are cut to about equal AREA of the
+  // upper triangle, at least MB200_GRM_PASSES (default 3) per device so that the download of one
+  // band overlaps the GEMM of the next, and dealt round-robin to the devices.
   long tile_rows = 1L << 40;
   if (const char *e = getenv("TILE_SIZE")) {
     const long v = atol(e);
-    if (v > 0) tile_rows = v < 128 ? 128 : v / 128 * 128;
+    if (v > 0) tile_rows = v < 256 ? 256 : v / 256 * 256;
   }
   double acc_gb = 16.0;
   if (const char *e = getenv("MB200_GRM_ACC_GB")) acc_gb = atof(e) > 0 ? atof(e) : acc_gb;
   const long mem_rows = (long)(acc_gb * 1073741824.0 / 4.0 / (double)rows_pad) / 256 * 256;
   if (mem_rows < tile_rows) tile_rows = mem_rows < 256 ? 256 : mem_rows;
-  const long tiles_per_dev = ceil_div(Mt, N);
-  long passes = ceil_div(tiles_per_dev * 128, tile_rows);
-  if (const char *e = getenv("MB200_GRM_PASSES")) passes = atol(e) > passes ? atol(e) : passes;
-  else if (passes < 3) passes = 3;
-  while (passes > 1 && N * passes * 4 > Mt && ceil_div(tiles_per_dev * 128, tile_rows) < passes) passes--;
-  if (N * passes > Mt) passes = ceil_div(Mt, N);
-  const int nparts = (int)(N * passes);
-  long acc_rows = 0;  // rows of the largest partition, padded to whole CTA pairs
-  for (int p = 0; p < nparts; p++) {
-    const long lr = round_up(crossprod_partition_rows(rows, p, nparts), 256);
-    acc_rows = lr > acc_rows ? lr : acc_rows;
+  long passes = 3;
+  if (const char *e = getenv("MB200_GRM_PASSES")) passes = atol(e) > 0 ? atol(e) : passes;
+  const long Nt = ceil_div(rows, 256);
+  std::vector<int> band_begin;  // in 128-row tiles; band b = [band_begin[b], band_begin[b + 1])
+  {
+    double area = 0.0;          // column tiles (of 256) at or right of the diagonal, per tile pair
+    for (long pr = 0; pr < Nt; pr++) area += (double)(Nt - pr);
+    const double target = area / (double)(N * passes);
+    double acc = 0.0;
+    band_begin.push_back(0);
+    for (long pr = 0; pr < Nt; pr++) {  // pr = pair of row tiles (2 pr, 2 pr + 1)
+      acc += (double)(Nt - pr);
+      const long height = (pr + 1) * 256 - (long)band_begin.back() * 128;
+      if (pr + 1 < Nt && (acc >= target || height + 256 > tile_rows)) {
+        band_begin.push_back((int)(2 * (pr + 1)));
+        acc = 0.0;
+      }
+    }
+    band_begin.push_back((int)Mt);
   }
-  // chunk of row tiles that is finished and downloaded at once: two orientations, two buffers
-  double chunk_mb = 128.0;
+  const int nbands = (int)band_begin.size() - 1;
+  long acc_rows = 0;  // rows of the tallest band, padded to whole CTA pairs
+  for (int b = 0; b < nbands; b++) {
+    const long h = round_up((long)(band_begin[b + 1] - band_begin[b]) * 128, 256);
+    acc_rows = h > acc_rows ? h : acc_rows;
+  }
+  // chunk of band rows that is finished and downloaded at once (two orientations, two buffers):
+  // at least 512 rows, so the transposed copy moves segments of >= 4 KB
+  double chunk_mb = 256.0;
   if (const char *e = getenv("MB200_GRM_CHUNK_MB")) chunk_mb = atof(e) > 0 ? atof(e) : chunk_mb;
-  long chunk_tiles = (long)(chunk_mb * 1048576.0 / (128.0 * 8.0 * (double)rows));
-  if (chunk_tiles < 1) chunk_tiles = 1;
-  if (chunk_tiles > acc_rows / 128) chunk_tiles = acc_rows / 128;
-  const long chunk_rows = chunk_tiles * 128;
+  long chunk_rows = (long)(chunk_mb * 1048576.0 / (8.0 * (double)rows)) / 256 * 256;
+  const long min_chunk = getenv("MB200_GRM_CHUNK_MB") ? 256 : 512;  // an explicit setting may go lower (tests)
+  if (chunk_rows < min_chunk) chunk_rows = min_chunk;
+  if (chunk_rows > acc_rows) chunk_rows = acc_rows;
 
   const bool ans_pin = host_is_pinned(ans), x_pin = host_is_pinned(x);
   std::vector<DevCtx> ctx(N);
@@ -196,7 +235,7 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     MB_CUDA(cudaMalloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad));
     for (int b = 0; b < 2; b++) {
       MB_CUDA(cudaMalloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows));
-      MB_CUDA(cudaMalloc(&c.PT[b], sizeof(double) * (size_t)chunk_rows * rows));
+      MB_CUDA(cudaMalloc(&c.PT[b], sizeof(double) * (size_t)chunk_rows * rows));  // both: crows x (n - c0) <= this
     }
     if (mode == 1) {
       MB_CUDA(cudaMalloc(&c.d_m, sizeof(double) * (rows + 8)));
@@ -217,37 +256,28 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     }
     MB_CUDA(cudaEventRecord(c.t0, c.s_main));
     if (mode == 1) MB_CHECK(crossprod_row_sums(c.d_x, k, rows, is_plink, c.d_f, do_scale, c.d_m, c.s_main));
-    // 2./3. passes
+    // 2./3. my bands
     int buf = 0;
     bool used[2] = {false, false};
-    for (long t = 0; t < passes; t++) {
-      const int part = (int)(g + N * t);
-      const long lrows = crossprod_partition_rows(rows, part, nparts);
-      if (lrows == 0) continue;
-      MB_CHECK(crossprod_partition_counts(c.d_x, k, rows, is_plink, part, nparts, c.C32, c.s_main, &c.ops));
-      for (long lr0 = 0; lr0 < lrows; lr0 += chunk_rows, buf ^= 1) {
-        const long crows = lrows - lr0 < chunk_rows ? lrows - lr0 : chunk_rows;
+    for (int b = g; b < nbands; b += N) {
+      const int tb = band_begin[b], te = band_begin[b + 1];
+      const long b0 = (long)tb * 128, b1 = (long)te * 128 < rows ? (long)te * 128 : rows;
+      MB_CHECK(crossprod_band_counts(c.d_x, k, rows, is_plink, tb, te, c.C32, c.s_main, &c.ops));
+      for (long c0 = b0; c0 < b1; c0 += chunk_rows, buf ^= 1) {
+        const long crows = b1 - c0 < chunk_rows ? b1 - c0 : chunk_rows;  // real rows (the last may be ragged)
+        const long w = rows - c0;
         if (used[buf]) MB_CUDA(cudaStreamWaitEvent(c.s_main, c.freed[buf], 0));  // its last download is done
-        dim3 grid((unsigned)ceil_div(rows, FC_T), (unsigned)(crows / FC_T));
-        finish_chunk_kernel<<<grid, 256, 0, c.s_main>>>(c.C32, rows_pad, lr0, crows, rows, part, nparts,
-                                                        mode == 1, do_scale, c.d_m, c.d_m ? c.d_m + rows : nullptr,
-                                                        c.P[buf], c.PT[buf]);
+        dim3 grid((unsigned)ceil_div(w, FC_T), (unsigned)ceil_div(crows, FC_T));
+        finish_chunk_kernel<<<grid, 256, 0, c.s_main>>>(c.C32, rows_pad, b0, c0, crows, rows, mode == 1, do_scale,
+                                                        c.d_m, c.d_m ? c.d_m + rows : nullptr, c.P[buf], c.PT[buf]);
         count_launch();
         MB_LAUNCH_CHECK();
         MB_CUDA(cudaEventRecord(c.fin[buf], c.s_main));
         MB_CUDA(cudaStreamWaitEvent(c.s_copy, c.fin[buf], 0));
-        for (long lt = lr0 / 128; lt < (lr0 + crows) / 128; lt++) {
-          const long mi = lt * nparts + part, i0 = mi * 128;
-          if (i0 >= rows) break;
-          const long first = (mi & ~1L) * 128, trows = rows - i0 < 128 ? rows - i0 : 128;
-          const long lo = (lt * 128 - lr0);  // row of this tile inside the chunk
-          // rows of the panel = columns of ans from `first` down
-          MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + first + i0 * rows, rows, c.P[buf] + lo * rows + first,
-                             rows, rows - first, (int)trows, c.s_copy));
-          // transposed panel = rows i of the columns right of `first`
-          MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + i0 + first * rows, rows, c.PT[buf] + lo + first * crows,
-                             crows, trows, (int)(rows - first), c.s_copy));
-        }
+        // rows of the panel = columns c0.. of ans, from row c0 down (contiguous runs of n - c0)
+        MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.P[buf], w, w, (int)crows, c.s_copy));
+        // transposed panel = rows c0.. of the columns from c0 on (runs of crows)
+        MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.PT[buf], crows, crows, (int)w, c.s_copy));
         MB_CUDA(cudaEventRecord(c.freed[buf], c.s_copy));
         used[buf] = true;
       }

@@ -411,6 +411,30 @@ int build_tile_list(long rows, int part, int nparts, TileCoord **d_tiles, int *n
   return 0;
 }
 
+// Tile list of a BAND of consecutive row tiles [tile_begin, tile_end) against all column tiles at
+// or right of the diagonal (the out-of-core host path, crossprod_host.cu: a band's rows are
+// consecutive rows of the result, so its panels leave for the host as large contiguous copies).
+// Output row tile mo = mi - tile_begin.  pair: CTA pairs over (mi, mi + 1); tile_begin must be even.
+int build_band_tile_list(long rows, int tile_begin, int tile_end, TileCoord **d_tiles, int *num_tiles,
+                         cudaStream_t stream, int *real_tiles, int pair) {
+  const int Mt = (int)ceil_div(rows, TC_BM), Nt = (int)ceil_div(rows, TC_BN);
+  if (tile_end > Mt) tile_end = Mt;
+  std::vector<TileCoord> v;
+  const int step = pair ? 2 : 1;
+  for (int sn = 0; sn < Nt; sn += 8)
+    for (int sm = tile_begin; sm < tile_end; sm += 16)
+      for (int nj = sn; nj < sn + 8 && nj < Nt; nj++)
+        for (int mi = sm; mi < sm + 16 && mi < tile_end; mi += step)
+          if ((long)TC_BN * (nj + 1) > (long)TC_BM * mi) v.push_back({mi, nj, mi - tile_begin, 0, -1, -1});
+  *num_tiles = (int)v.size();
+  if (real_tiles) *real_tiles = pair ? 2 * (int)v.size() : (int)v.size();
+  if (v.empty()) v.push_back({0, 0, 0, 0, -1, -1});
+  MB_CUDA(pool_alloc(d_tiles, sizeof(TileCoord) * v.size(), stream));
+  MB_CUDA(cudaMemcpyAsync(*d_tiles, v.data(), sizeof(TileCoord) * v.size(), cudaMemcpyHostToDevice, stream));
+  MB_CUDA(cudaStreamSynchronize(stream));  // v goes out of scope
+  return 0;
+}
+
 // Work items one launch keeps in flight: CTAs (one per SM) or CTA pairs (clusters of 2).
 int crossprod_tc_units(int sm_count, int pair) {
   if (!pair) return sm_count;

@@ -179,6 +179,8 @@ __device__ __forceinline__ void group_bar_sync(int g) {  // named barrier 1 + g,
 // of the pipeline off (no clock64 bookkeeping, no run-time branches in the hot loops -- a run-time
 // switch alone cost 7 %): 1 = no tcgen05.st, 2 = no MMAs, 4 = no expansion ALU (the raw words are
 // stored).  Results are garbage; timing only.  PROBE < 0: the product kernel (TRACE: p.dbg bits).
+// PROBE == 8: an encoding experiment with CORRECT results -- the A operand carries the genotype
+// itself (0/1/2, right shifts) instead of 64 x genotype (left shifts).
 template <bool TRACE, int PROBE>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
@@ -203,7 +205,7 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.R;
   const int stride = gridDim.x;
-  const int dbg = PROBE >= 0 ? PROBE : (TRACE ? p.dbg : 0);
+  const int dbg = PROBE >= 0 ? (PROBE & 7) : (TRACE ? p.dbg : 0);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < DT_RMAX * DT_ZSLOTS; i++) mbar_init(&z_full[i], 1);
@@ -314,7 +316,7 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
       const int r = 32 * w + lane;
       const uint32_t lane_base = tmem_base + ((uint32_t)(32 * w) << 16);
       const uint32_t a_col = acol0 + g * DT_ASLOTS * 32;
-      const int P = 8 * p.S - 2 + 6;  // + 6: the A operand carries 64 x genotype
+      const int P = 8 * p.S - 2 + (PROBE == 8 ? 0 : 6);  // + 6: the A operand carries 64 x genotype
       uint8_t *zslots = zring + g * DT_ZSLOTS * DT_ZBYTES;
       uint64_t *zf = z_full + g * DT_ZSLOTS;
       uint64_t *af = a_full + g * DT_ASLOTS, *ae = a_empty + g * DT_ASLOTS;
@@ -379,6 +381,11 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
           if (dbg & 4) {
 #pragma unroll
             for (int i = 0; i < 32; i++) a[i] = wds[i >> 2];
+          } else if (PROBE == 8) {
+#pragma unroll
+            for (int qq = 0; qq < 8; qq++)
+#pragma unroll
+              for (int j = 0; j < 4; j++) a[4 * qq + j] = (wds[qq] >> (2 * j)) & 0x03030303u;
           } else {
 #pragma unroll
             for (int qq = 0; qq < 8; qq++)
@@ -528,7 +535,7 @@ static const TcEnv &tc_env() {
     TcEnv v;
     if (const char *e = getenv("MB200_TRACE")) v.trace = atoi(e) > 0;
     if (const char *e = getenv("MB200_DBG")) v.dbg = atoi(e);
-    if (const char *e = getenv("MB200_PROBE")) v.probe = atoi(e) & 7;
+    if (const char *e = getenv("MB200_PROBE")) v.probe = atoi(e) < 0 || atoi(e) > 8 ? 0 : atoi(e);
     if (const char *e = getenv("MB200_DGEMM_TOL")) v.tol = atof(e) > 0 ? atof(e) : v.tol;
     if (const char *e = getenv("MB200_TC_FLAGS")) v.flags = atoi(e);
     return v;
@@ -540,11 +547,12 @@ static const TcEnv &tc_env() {
 // device this process launches the kernel on (single-process multi-GPU handles, multi.cu).
 typedef void (*DtKernel)(CUtensorMap, CUtensorMap, DtParams);
 static DtKernel dt_probe_kernel(int bits) {
-  static const DtKernel k[8] = {dgemm_tc_kernel<false, 0>, dgemm_tc_kernel<false, 1>,
+  static const DtKernel k[9] = {dgemm_tc_kernel<false, 0>, dgemm_tc_kernel<false, 1>,
                                 dgemm_tc_kernel<false, 2>, dgemm_tc_kernel<false, 3>,
                                 dgemm_tc_kernel<false, 4>, dgemm_tc_kernel<false, 5>,
-                                dgemm_tc_kernel<false, 6>, dgemm_tc_kernel<false, 7>};
-  return k[bits & 7];
+                                dgemm_tc_kernel<false, 6>, dgemm_tc_kernel<false, 7>,
+                                dgemm_tc_kernel<false, 8>};
+  return k[bits < 0 || bits > 8 ? 0 : bits];
 }
 static int tc_prepare_device(int device) {
   static std::atomic<unsigned long long> done{0};
@@ -553,7 +561,7 @@ static int tc_prepare_device(int device) {
                                dt_smem_bytes(DT_NMAX)));
   MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                dt_smem_bytes(DT_NMAX)));
-  for (int b = 0; b < 8; b++)
+  for (int b = 0; b <= 8; b++)
     MB_CUDA(cudaFuncSetAttribute(dt_probe_kernel(b), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  dt_smem_bytes(DT_NMAX)));
   if (device >= 0 && device < 64) done.fetch_or(1ull << device, std::memory_order_release);

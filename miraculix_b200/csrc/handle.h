@@ -146,8 +146,8 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
                      CrossprodTiming *timing);
 
 long crossprod_partition_rows(long rows, int part, int nparts);
-int crossprod_partition_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int part,
-                               int nparts, int32_t *C32, cudaStream_t stream, double *executed_ops);
+int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int tile_begin,
+                          int tile_end, int32_t *C32, cudaStream_t stream, double *executed_ops);
 int crossprod_row_sums(const uint8_t *d_x, long k, long rows, int is_plink_format, const double *d_f,
                        int do_scale, double *d_m, cudaStream_t stream);
 int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,

@@ -34,3 +34,4 @@ run st_only       MB200_PROBE=6                  # TMA + LDS + st (raw words); n
 run s8_full       MB200_DGEMM_SLICES=8
 run s4_full       MB200_DGEMM_SLICES=4
 NCOL=2 run ncol2_full MB200_X=0
+run lowbits_full  MB200_PROBE=8                  # everything on, A operand = genotype 0/1/2 (correct results)
