@@ -364,11 +364,31 @@ int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_pli
 int build_band_tile_list(long rows, int tile_begin, int tile_end, TileCoord **d_tiles, int *num_tiles,
                          cudaStream_t stream, int *real_tiles, int pair);
 
-int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int tile_begin,
-                          int tile_end, int32_t *C32, cudaStream_t stream, double *executed_ops) {
-  if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
+int crossprod_band_plan(long rows, int tile_begin, int tile_end, cudaStream_t stream, BandPlan *plan) {
   if (tile_begin < 0 || tile_end <= tile_begin || (tile_begin & 1))
     return fail(-2, __func__, __LINE__, "bad band [%d, %d)", tile_begin, tile_end);
+  if (options().crossprod_mode < 1)
+    return fail(-2, __func__, __LINE__, "the tiled host path needs the tensor-core crossproduct (mode 1 or 2)");
+  int device = 0;
+  MB_CUDA(cudaGetDevice(&device));
+  const int sms = device_sm_count(device);
+  plan->pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? 1 : 0;
+  plan->tile_begin = tile_begin;
+  plan->tile_end = tile_end;
+  TileCoord *d_tiles = nullptr;
+  MB_CHECK(build_band_tile_list(rows, tile_begin, tile_end, &d_tiles, &plan->num_tiles, stream,
+                                &plan->real_tiles, plan->pair));
+  plan->d_tiles = d_tiles;
+  return 0;
+}
+void crossprod_band_plan_free(BandPlan *plan, cudaStream_t stream) {
+  if (plan->d_tiles) cudaFreeAsync(plan->d_tiles, stream);
+  plan->d_tiles = nullptr;
+}
+
+int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, const BandPlan &plan,
+                          int32_t *C32, cudaStream_t stream, double *executed_ops) {
+  if (rows <= 0 || k <= 0) return fail(-2, __func__, __LINE__, "empty matrix (%ld x %ld)", rows, k);
   int device = 0;
   MB_CUDA(cudaGetDevice(&device));
   const int sms = device_sm_count(device);
@@ -382,13 +402,9 @@ int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_fo
   const long kpad = slab_kbytes * 4;
   if (is_plink_format) MB_CHECK(upload_lut());
   int8_t *X8 = nullptr;
-  TileCoord *d_tiles = nullptr;
-  int num_tiles = 0, real_tiles = 0;
   CallScratch scratch(stream);
   MB_CUDA(scratch.alloc(&X8, (size_t)rows_pad * kpad));
-  const int pair = options().crossprod_mode == 2 && crossprod_tc_units(sms, 1) > 0 ? 1 : 0;
-  MB_CHECK(build_band_tile_list(rows, tile_begin, tile_end, &d_tiles, &num_tiles, stream, &real_tiles, pair));
-  scratch.adopt(d_tiles);
+  const TileCoord *d_tiles = static_cast<const TileCoord *>(plan.d_tiles);
   int slab = 0;
   for (long kb0 = 0; kb0 < nb; kb0 += slab_kbytes, slab++) {
     const long kbytes = nb - kb0 < slab_kbytes ? nb - kb0 : slab_kbytes;
@@ -396,13 +412,9 @@ int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_fo
     expand_2bit_launch(d_x, rows, nb, kb0, kbytes, is_plink_format, X8, rows_pad, kpad, sms, stream);
     count_launch();
     MB_LAUNCH_CHECK();
-    if (options().crossprod_mode >= 1) {
-      MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, num_tiles, C32, rows_pad, slab > 0,
-                                   sms, stream, nullptr, 0, pair));
-      if (executed_ops) *executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)real_tiles;
-    } else {
-      return fail(-2, __func__, __LINE__, "the tiled host path needs the tensor-core crossproduct (mode 1 or 2)");
-    }
+    MB_CHECK(crossprod_tc_launch(X8, rows_pad, kuse, kpad, d_tiles, plan.num_tiles, C32, rows_pad, slab > 0,
+                                 sms, stream, nullptr, 0, plan.pair));
+    if (executed_ops) *executed_ops += 2.0 * 128.0 * 256.0 * (double)kuse * (double)plan.real_tiles;
   }
   return 0;  // `scratch` frees stream-ordered: the slab outlives the kernels enqueued above
 }

@@ -19,6 +19,7 @@
 // Pageable `ans` / `x` (Julia, Fortran arrays) go through the pinned ring of stager.h.
 #include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <memory>
 #include "common.cuh"
 #include "multi.h"
@@ -94,20 +95,23 @@ struct DevCtx {
   cudaEvent_t fin[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr}, up = nullptr;
   cudaEvent_t t0 = nullptr, t1 = nullptr;
   Stager stager;
+  std::vector<BandPlan> plans;
   double ops = 0.0;
   void release() {
+    for (BandPlan &p : plans) crossprod_band_plan_free(&p, s_main);
     if (s_main) cudaStreamSynchronize(s_main);
     if (s_copy) cudaStreamSynchronize(s_copy);
-    cudaFree(d_x);
-    cudaFree(d_f);
-    cudaFree(d_m);
-    cudaFree(C32);
+    if (d_x) cudaFreeAsync(d_x, s_main);
+    if (d_f) cudaFreeAsync(d_f, s_main);
+    if (d_m) cudaFreeAsync(d_m, s_main);
+    if (C32) cudaFreeAsync(C32, s_main);
     for (int b = 0; b < 2; b++) {
-      cudaFree(P[b]);
-      cudaFree(PT[b]);
+      if (P[b]) cudaFreeAsync(P[b], s_main);
+      if (PT[b]) cudaFreeAsync(PT[b], s_main);
       if (fin[b]) cudaEventDestroy(fin[b]);
       if (freed[b]) cudaEventDestroy(freed[b]);
     }
+    if (s_main) cudaStreamSynchronize(s_main);
     if (up) cudaEventDestroy(up);
     if (t0) cudaEventDestroy(t0);
     if (t1) cudaEventDestroy(t1);
@@ -202,6 +206,10 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
   if (chunk_rows > acc_rows) chunk_rows = acc_rows;
 
   const bool ans_pin = host_is_pinned(ans), x_pin = host_is_pinned(x);
+  const auto w0 = std::chrono::steady_clock::now();
+  auto since = [&](void) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count(); };
+  debug_info("crossproduct %ld x %ld: %d device(s), %d band(s), accumulator %ld rows, chunks of %ld rows, ans %s, x %s",
+             rows, k, N, nbands, acc_rows, chunk_rows, ans_pin ? "pinned" : "pageable", x_pin ? "pinned" : "pageable");
   std::vector<DevCtx> ctx(N);
   Team team(N);
   // slices of the packed rows each device uploads itself
@@ -231,19 +239,26 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     MB_CUDA(cudaEventCreate(&c.t0));
     MB_CUDA(cudaEventCreate(&c.t1));
     if (!ans_pin || !x_pin) MB_CHECK(c.stager.init(4u << 20));
-    MB_CUDA(cudaMalloc(&c.d_x, (size_t)rows * nb));
-    MB_CUDA(cudaMalloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad));
+    // scratch from the library's pool (cached between calls: a GBLUP script calls this repeatedly)
+    MB_CUDA(pool_alloc(&c.d_x, (size_t)rows * nb, c.s_main));
+    MB_CUDA(pool_alloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad, c.s_main));
     for (int b = 0; b < 2; b++) {
-      MB_CUDA(cudaMalloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows));
-      MB_CUDA(cudaMalloc(&c.PT[b], sizeof(double) * (size_t)chunk_rows * rows));  // both: crows x (n - c0) <= this
+      MB_CUDA(pool_alloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows, c.s_main));
+      MB_CUDA(pool_alloc(&c.PT[b], sizeof(double) * (size_t)chunk_rows * rows, c.s_main));  // both: crows x (n - c0) <= this
     }
     if (mode == 1) {
-      MB_CUDA(cudaMalloc(&c.d_m, sizeof(double) * (rows + 8)));
+      MB_CUDA(pool_alloc(&c.d_m, sizeof(double) * (rows + 8), c.s_main));
       if (f) {
-        MB_CUDA(cudaMalloc(&c.d_f, sizeof(double) * k));
+        MB_CUDA(pool_alloc(&c.d_f, sizeof(double) * k, c.s_main));
         MB_CUDA(cudaMemcpyAsync(c.d_f, f, sizeof(double) * k, cudaMemcpyHostToDevice, c.s_main));
       }
     }
+    // work lists of my bands, uploaded while the stream is still empty (the upload synchronises it)
+    for (int b = g; b < nbands; b += N) {
+      c.plans.emplace_back();
+      MB_CHECK(crossprod_band_plan(rows, band_begin[b], band_begin[b + 1], c.s_main, &c.plans.back()));
+    }
+    if (g == 0) debug_info("  setup (streams, pool scratch, work lists) done at %.2f ms", since());
     // 1. my rows of the packed matrix from the host, the rest from the peers
     MB_CHECK(upload_bytes(c, x_pin, c.d_x + xr0[g] * nb, x + xr0[g] * nb, (size_t)(xr0[g + 1] - xr0[g]) * nb));
     MB_CUDA(cudaEventRecord(c.up, c.s_main));
@@ -259,10 +274,11 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     // 2./3. my bands
     int buf = 0;
     bool used[2] = {false, false};
-    for (int b = g; b < nbands; b += N) {
+    size_t pi = 0;
+    for (int b = g; b < nbands; b += N, pi++) {
       const int tb = band_begin[b], te = band_begin[b + 1];
       const long b0 = (long)tb * 128, b1 = (long)te * 128 < rows ? (long)te * 128 : rows;
-      MB_CHECK(crossprod_band_counts(c.d_x, k, rows, is_plink, tb, te, c.C32, c.s_main, &c.ops));
+      MB_CHECK(crossprod_band_counts(c.d_x, k, rows, is_plink, c.plans[pi], c.C32, c.s_main, &c.ops));
       for (long c0 = b0; c0 < b1; c0 += chunk_rows, buf ^= 1) {
         const long crows = b1 - c0 < chunk_rows ? b1 - c0 : chunk_rows;  // real rows (the last may be ragged)
         const long w = rows - c0;
@@ -283,9 +299,11 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
       }
     }
     MB_CUDA(cudaEventRecord(c.t1, c.s_main));
+    if (g == 0) debug_info("  all work enqueued at %.2f ms", since());
     if (!ans_pin) MB_CHECK(c.stager.drain());
     MB_CUDA(cudaStreamSynchronize(c.s_main));
     MB_CUDA(cudaStreamSynchronize(c.s_copy));
+    if (g == 0) debug_info("  streams drained at %.2f ms", since());
     // peers may still be pulling my slice of the input
     return team.barrier();
   });
@@ -303,6 +321,7 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     ctx[g].release();
     return 0;
   });
+  debug_info("  released at %.2f ms", since());
   return rc;
 }
 

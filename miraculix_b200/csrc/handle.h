@@ -146,8 +146,16 @@ int crossprod_device(const uint8_t *d_x, long k, long rows, int is_plink_format,
                      CrossprodTiming *timing);
 
 long crossprod_partition_rows(long rows, int part, int nparts);
-int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, int tile_begin,
-                          int tile_end, int32_t *C32, cudaStream_t stream, double *executed_ops);
+// Work list of a band of row tiles, built and uploaded once (synchronises `stream`: do it before
+// the pipeline fills); freed stream-ordered by crossprod_band_plan_free.
+struct BandPlan {
+  void *d_tiles = nullptr;
+  int num_tiles = 0, real_tiles = 0, pair = 0, tile_begin = 0, tile_end = 0;
+};
+int crossprod_band_plan(long rows, int tile_begin, int tile_end, cudaStream_t stream, BandPlan *plan);
+void crossprod_band_plan_free(BandPlan *plan, cudaStream_t stream);
+int crossprod_band_counts(const uint8_t *d_x, long k, long rows, int is_plink_format, const BandPlan &plan,
+                          int32_t *C32, cudaStream_t stream, double *executed_ops);
 int crossprod_row_sums(const uint8_t *d_x, long k, long rows, int is_plink_format, const double *d_f,
                        int do_scale, double *d_m, cudaStream_t stream);
 int crossprod_partition_device(const uint8_t *d_x, long k, long rows, int is_plink_format, int mode,
