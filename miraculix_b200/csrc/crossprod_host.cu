@@ -101,7 +101,7 @@ struct DevCtx {
     for (BandPlan &p : plans) crossprod_band_plan_free(&p, s_main);
     if (s_main) cudaStreamSynchronize(s_main);
     if (s_copy) cudaStreamSynchronize(s_copy);
-    if (d_x) cudaFreeAsync(d_x, s_main);
+    cudaFree(d_x);
     if (d_f) cudaFreeAsync(d_f, s_main);
     if (d_m) cudaFreeAsync(d_m, s_main);
     if (C32) cudaFreeAsync(C32, s_main);
@@ -240,7 +240,8 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     MB_CUDA(cudaEventCreate(&c.t1));
     if (!ans_pin || !x_pin) MB_CHECK(c.stager.init(4u << 20));
     // scratch from the library's pool (cached between calls: a GBLUP script calls this repeatedly)
-    MB_CUDA(pool_alloc(&c.d_x, (size_t)rows * nb, c.s_main));
+    // the packed matrix is read by the peers: plain cudaMalloc (pool memory is private to its device)
+    MB_CUDA(cudaMalloc(&c.d_x, (size_t)rows * nb));
     MB_CUDA(pool_alloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad, c.s_main));
     for (int b = 0; b < 2; b++) {
       MB_CUDA(pool_alloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows, c.s_main));

@@ -54,6 +54,9 @@ init_c_kernel(double *__restrict__ C, long ldc, long m, int n, const double *__r
   }
 }
 
+int dgemm_init_c(Handle *h, const DgemmView &v, int n, double *dC, long ldc, int centered,
+                 const double *w, const int *guard);
+
 DgemmView full_view(const Handle *h, int trans) {
   DgemmView v;
   v.trans = trans;
@@ -93,6 +96,12 @@ int dgemm_center_init(Handle *h, const DgemmView &v, int n, const double *dB, lo
     count_launch();
     MB_LAUNCH_CHECK();
   }
+  return dgemm_init_c(h, v, n, dC, ldc, centered, w, guard);
+}
+
+// C (+)= w y^T from centring scalars that are already computed (dgemm_tc.cu col_stats_kernel)
+int dgemm_init_c(Handle *h, const DgemmView &v, int n, double *dC, long ldc, int centered,
+                 const double *w, const int *guard) {
   if (centered || !v.accumulate) {
     init_c_kernel<<<(unsigned)ceil_div(v.rows, 256), 256, 0, h->stream>>>(
         dC, ldc, v.rows, n, w, v.y, centered, v.accumulate, guard);

@@ -18,6 +18,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <memory>
 #include <new>
 #include "../../include/miraculix_b200.h"
@@ -25,6 +26,18 @@
 #include "team.h"
 
 namespace mb200 {
+
+// PRINT_LEVEL > 0: wall-clock phases of worker 0 (the reference prints its own timings the same
+// way, snp_multiply_cuda.cu:354-366)
+struct PhaseClock {
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  bool on;
+  explicit PhaseClock(bool enabled) : on(enabled && print_level() > 0) {}
+  void mark(const char *what) {
+    if (!on) return;
+    debug_info("    %-34s %.3f ms", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  }
+};
 
 int cg_solve_device(Handle *h, const double *d_b, double *d_x, double lambda, double tol,
                     int max_iter, mb200_allreduce_fn ar, void *user, int *iters, double *resid);
@@ -356,6 +369,7 @@ static int dgemm_n_pass(MultiHandle *m, int g, int n, const double *B, long ldb,
                         int S) {
   Handle *h = m->shard[g];
   const bool c_pin = host_is_pinned(C);
+  PhaseClock pc(g == 0);
   if (options().dgemm_mode == 1) {
     TcExternal ext;
     ext.S = S;
@@ -368,8 +382,10 @@ static int dgemm_n_pass(MultiHandle *m, int g, int n, const double *B, long ldb,
                        m->s_count[g], n, h->stream));
     MB_CHECK(dgemm_device(h, 0, n, h->d_B, m->s_count[g], h->d_C, m->indiv));
   }
+  pc.mark("'N' partial enqueued");
   MB_CUDA(cudaMemsetAsync(m->d_chk[g], 0, 2 * sizeof(unsigned long long) * m->max_n, h->stream));
   MB_CHECK(exchange_point(m, g, m->phase, h->stream));
+  pc.mark("'N' exchange point passed");
   const long rows = m->i_count[g];
   if (rows > 0) {
     long blocks = ceil_div(rows * n, 256);
@@ -387,8 +403,11 @@ static int dgemm_n_pass(MultiHandle *m, int g, int n, const double *B, long ldb,
   if (!c_pin && rows > 0) MB_CHECK(h->stager.drain());
   MB_CUDA(cudaStreamSynchronize(h->stream));
   MB_CUDA(cudaStreamSynchronize(h->copy_stream));
+  pc.mark("'N' streams drained");
   // nobody overwrites a partial (next pass, next call) before every peer has read it
-  return m->team->barrier();
+  const int brc = m->team->barrier();
+  pc.mark("'N' final barrier");
+  return brc;
 }
 
 // The test of decide_kernel (dgemm_tc.cu) on the reduced result; identical on every worker.
@@ -428,6 +447,7 @@ static int dgemm_n_worker(MultiHandle *m, int g, int n, const double *B, long ld
 static int dgemm_t_worker(MultiHandle *m, int g, int n, const double *B, long ldb, double *C, long ldc) {
   Handle *h = m->shard[g];
   const bool b_pin = host_is_pinned(B);
+  PhaseClock pc(g == 0);
   if (!b_pin) MB_CHECK(h->stager.init(4u << 20));
   // my 1/N of the replicated B, then the peers' slices over NVLink
   MB_CHECK(panel_h2d(&h->stager, b_pin, h->d_B + m->i_begin[g], m->indiv, B + m->i_begin[g], ldb,
@@ -450,8 +470,10 @@ static int dgemm_t_worker(MultiHandle *m, int g, int n, const double *B, long ld
     count_launch();
     MB_LAUNCH_CHECK();
   }
+  pc.mark("'T' slice up, gather enqueued");
   if (options().dgemm_mode == 1) {
     MB_CHECK(dgemm_tc_host_pipelined(h, 1, n, h->d_B, m->indiv, C + m->s_begin[g], ldc, 1, 0, nullptr));
+    pc.mark("'T' product + download done");
   } else {
     const bool c_pin = host_is_pinned(C);
     if (!c_pin) MB_CHECK(h->stager.init(4u << 20));

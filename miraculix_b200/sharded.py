@@ -109,6 +109,19 @@ class ShardedCompressed:
             self._stream = torch.cuda.ExternalStream(ptr)
         return self._stream
 
+    def _fork(self):
+        """Order the library's stream after the caller's current torch stream (inputs produced
+        there are complete before our kernels read them)."""
+        import torch
+        if self.handle is not None and torch.cuda.is_available():
+            self.stream().wait_stream(torch.cuda.current_stream())
+
+    def _join(self):
+        """... and the caller's stream after ours (later torch ops see finished results)."""
+        import torch
+        if self.handle is not None and torch.cuda.is_available():
+            torch.cuda.current_stream().wait_stream(self.stream())
+
     def _device_dgemm(self, trans: int, B, Cout) -> None:
         from . import api
         lib = api.load_library()
@@ -123,23 +136,37 @@ class ShardedCompressed:
     def dgemm_n(self, B_local, C_out):
         """B_local: (n, |S_g|) this rank's rows of B; C_out: (n, indiv) -- the full product."""
         import torch.distributed as dist
+        cuda = bool(getattr(C_out, "is_cuda", False))
+        if cuda:
+            self._fork()
         if self.s_count > 0:
             self._local(0, B_local, C_out)
+        elif cuda and self.handle is not None:
+            import torch
+            with torch.cuda.stream(self.stream()):
+                C_out.zero_()
         else:
             C_out.zero_()
         if self.world > 1:
-            if C_out.is_cuda:
+            if cuda and self.handle is not None:
                 import torch
                 with torch.cuda.stream(self.stream()):
                     dist.all_reduce(C_out, op=dist.ReduceOp.SUM, group=self.group)
             else:
                 dist.all_reduce(C_out, op=dist.ReduceOp.SUM, group=self.group)
+        if cuda:
+            self._join()
         return C_out
 
     def dgemm_t(self, B, C_local):
         """B: (n, indiv) replicated; C_local: (n, |S_g|) rows S_g of the result.  No exchange."""
+        cuda = bool(getattr(C_local, "is_cuda", False))
+        if cuda:
+            self._fork()
         if self.s_count > 0:
             self._local(1, B, C_local)
+        if cuda:
+            self._join()
         return C_local
 
     # -- the same two directions with HOST panels (pinned CPU tensors) -------------------------
@@ -154,6 +181,7 @@ class ShardedCompressed:
         from . import api
         lib = api.load_library()
         n = hB_local.shape[0]
+        self._fork()
         if self.s_count > 0:
             rc = lib.mb200_dgemm_compressed_mixed(0, self.handle, n, C.c_void_p(hB_local.data_ptr()),
                                                   hB_local.shape[1], 0, C.c_void_p(C_dev.data_ptr()),
@@ -165,6 +193,7 @@ class ShardedCompressed:
             if self.world > 1:
                 dist.all_reduce(C_dev, op=dist.ReduceOp.SUM, group=self.group)
             hC.copy_(C_dev, non_blocking=True)
+        self._join()
         return hC
 
     def dgemm_t_host(self, hB, hC_local):
@@ -211,4 +240,7 @@ class ShardedCompressed:
                     return 1
 
             hook = api.ALLREDUCE_FN(_allreduce)
-        return api.cg_solve_device(self.handle, b.data_ptr(), x.data_ptr(), lam, tol, max_iter, hook)
+        self._fork()
+        out = api.cg_solve_device(self.handle, b.data_ptr(), x.data_ptr(), lam, tol, max_iter, hook)
+        self._join()
+        return out

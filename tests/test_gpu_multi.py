@@ -394,3 +394,34 @@ def test_nonfinite_b_gives_nan_columns(gpu_lib):
                         assert relerr(got[:, [0, 2]], want[:, [0, 2]]) <= TOL, (tr, mode, bad)
             finally:
                 api.free_compressed(h)
+
+
+def test_concurrent_handles_on_one_device(gpu_lib):
+    """Four ordinary handles on one GPU driven from four host threads at once: the tensor-core
+    kernels of different handles share the device and must not disturb each other.  (Regression:
+    the TMA refill of a packed-Z slot could overtake the expanders' shared-memory loads of the
+    previous chunk when other kernels changed the timing -- sporadic wrong rows; fixed by a proxy
+    fence before the refill.)  Results must equal the sequential ones up to atomic summation order."""
+    import threading
+    from miraculix_b200 import api
+    snps, indiv, ncol, nthreads = 125_000, 40_000, 10, 4
+    hs = [api.simulate_compressed(snps, indiv, 500 + i, ncol) for i in range(nthreads)]
+    rng = np.random.default_rng(7)
+    B = {"N": np.asfortranarray(rng.standard_normal((snps, ncol))),
+         "T": np.asfortranarray(rng.standard_normal((indiv, ncol)))}
+    try:
+        ref = [{d: api.dgemm_compressed(d, h, B[d], snps, indiv) for d in "NT"} for h in hs]
+        for rep in range(6):
+            out = [None] * nthreads
+
+            def work(i):
+                out[i] = {d: api.dgemm_compressed(d, hs[i], B[d], snps, indiv) for d in "NT"}
+            th = [threading.Thread(target=work, args=(i,)) for i in range(nthreads)]
+            [t.start() for t in th]
+            [t.join() for t in th]
+            for i in range(nthreads):
+                for d in "NT":
+                    assert relerr(out[i][d], ref[i][d]) <= 1e-12, (rep, i, d)
+    finally:
+        for h in hs:
+            api.free_compressed(h)
