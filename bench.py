@@ -439,6 +439,42 @@ def _wall_steps(fn, steps, warm):
     return sum(ts) / len(ts), min(ts)
 
 
+def host_link_probe(devices, mb=64, reps=4):
+    """Aggregate pinned host <-> device copy bandwidth with ALL `devices` copying at once (one
+    stream per device, 64 MB buffers): the floor of any e2e number is bytes / this.  On cloud
+    boxes the GPUs often share host links, so the aggregate does not grow with the device count."""
+    import torch
+    devs = sorted(set(devices))
+    out = {}
+    try:
+        hb = [torch.empty(mb << 20, dtype=torch.uint8).pin_memory() for _ in devs]
+        db = [torch.empty(mb << 20, dtype=torch.uint8, device=f"cuda:{d}") for d in devs]
+        st = [torch.cuda.Stream(device=f"cuda:{d}") for d in devs]
+        for name in ("h2d", "d2h"):
+            best = 0.0
+            for it in range(reps + 1):
+                for d in devs:
+                    torch.cuda.synchronize(d)
+                t0 = time.perf_counter()
+                for i, d in enumerate(devs):
+                    with torch.cuda.stream(st[i]):
+                        if name == "h2d":
+                            db[i].copy_(hb[i], non_blocking=True)
+                        else:
+                            hb[i].copy_(db[i], non_blocking=True)
+                for d in devs:
+                    torch.cuda.synchronize(d)
+                dt = time.perf_counter() - t0
+                if it:
+                    best = max(best, len(devs) * (mb << 20) / dt / 1e9)
+            out[name + "_gbs_aggregate"] = best
+        out["devices"] = devs
+        out["how"] = f"{mb} MB pinned buffer per device, all devices at once, best of {reps}, wall clock"
+    except Exception as exc:
+        out["error"] = repr(exc)
+    return out
+
+
 def run_e2e(args, lib, api, handle, devices, seed, hBn, hBt, Cn_dev, Ct_dev, steps):
     """dgemm_compressed() 'n' + 't' through the C ABI with host panels, one process.  handle: an
     existing single-device handle, or None = create a handle of the same simulated matrix over
@@ -490,8 +526,14 @@ def run_e2e(args, lib, api, handle, devices, seed, hBn, hBt, Cn_dev, Ct_dev, ste
     par_p = max(rel(torch.from_numpy(pCn), hCn), rel(torch.from_numpy(pCt), hCt))
     if own:
         lib.free_compressed(C.byref(handle))
+    link = host_link_probe(devices)
     units = 2.0 * snps * indiv * ncol
     nbytes = 8 * ncol * (snps + indiv)
+    floor_ms = None
+    if link.get("h2d_gbs_aggregate") and link.get("d2h_gbs_aggregate"):
+        # 'n' moves snps x ncol up and indiv x ncol down, 't' the reverse; the calls are sequential
+        floor_ms = (8e-6 * ncol * (snps / link["h2d_gbs_aggregate"] + indiv / link["d2h_gbs_aggregate"]) +
+                    8e-6 * ncol * (indiv / link["h2d_gbs_aggregate"] + snps / link["d2h_gbs_aggregate"]))
     return {"value": units / mean_s, "unit": UNIT, "h2d_bytes_per_step": nbytes,
             "d2h_bytes_per_step": nbytes, "steps": steps, "ms_per_step": mean_s * 1e3,
             "best_ms_per_step": best_s * 1e3, "n_ms": n_s * 1e3, "t_ms": t_s * 1e3,
@@ -500,6 +542,7 @@ def run_e2e(args, lib, api, handle, devices, seed, hBn, hBt, Cn_dev, Ct_dev, ste
                     "dgemm_compressed() C-ABI on ONE sharded handle: one process, %d device shards %s, "
                     "peer-memory all-gather ('t') / reduce-scatter ('n'), pinned host B/C" % (nsh, devices)),
             "devices": devices, "shards": nsh, "gpu_launches_per_step": int(launches),
+            "host_link": link, "host_link_floor_ms_per_step": floor_ms,
             "pageable": {"value": units / pmean_s, "ms_per_step": pmean_s * 1e3,
                          "best_ms_per_step": pbest_s * 1e3, "vs_pinned": pmean_s / mean_s,
                          "what": "the same calls with pageable numpy panels (staged through the "

@@ -22,6 +22,7 @@
 //   HBM-bound by design: algorithmic bytes = the packed matrix once (+ B, C).
 #include <cuda.h>
 #include <math.h>
+#include <chrono>
 #include <stdlib.h>
 #include "common.cuh"
 #include "handle.h"
@@ -788,6 +789,13 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   const bool b_pin = !b_dev && host_is_pinned(B), c_pin = !c_dev && host_is_pinned(C);
   Stager *sg = &h->stager;
   if ((!b_dev && !b_pin) || (!c_dev && !c_pin)) MB_CHECK(sg->init(4u << 20));
+  const auto w0 = std::chrono::steady_clock::now();
+  const bool trace_host = print_level() > 1;  // PRINT_LEVEL >= 2: host-side enqueue timeline
+  auto mark = [&](const char *what, int i) {
+    if (trace_host)
+      debug_info("      pipeline dev %d %-18s %d at %.3f ms", h->device, what, i,
+                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count());
+  };
   const DgemmView full = full_view(h, trans);
   bool adaptive = false, first_main = true;
   int S = tc_digits(n, full.rows, full.K, &adaptive);
@@ -844,10 +852,12 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
         MB_CHECK(panel_h2d(sg, b_pin, h->d_B + s0, k, B + s0, ldb, cnt, n, h->copy_stream));
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
         MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
+        mark("upload enqueued", i);
       }
       DgemmView v = sub_view(h, 0, s0, cnt);
       v.accumulate = i > 0;
       MB_CHECK(tc_pass(h, v, n, dB + s0, ldB, dC, ldC, S, 0, nullptr, tc_amax_all(h), &first_main, ev));
+      mark("kernels enqueued", i);
     }
     if (adaptive) MB_CHECK(tc_check(h, dC, ldC, m, n, S, tc_amax_all(h), full.rowsum_max));
     if (ext && ext->d_err) {
@@ -870,9 +880,11 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
       MB_CHECK(tc_pass(h, v, n, dB, ldB, dC + s0, ldC, S, 0, nullptr, nullptr, &first_main, ev));
       if (adaptive)
         MB_CHECK(tc_check(h, dC + s0, ldC, cnt, n, S, tc_scratch(h, 0).amaxB, v.rowsum_max));
+      mark("kernels enqueued", i);
       if (pipe_out) {
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->stream));
         if (i > 0) MB_CHECK(download(i - 1));
+        mark("download enqueued", i - 1);
       }
     }
     if (pipe_out) MB_CHECK(download(chunks - 1));
@@ -882,10 +894,12 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
     MB_CUDA(cudaMemcpyAsync(h_flag, tc_flag(h), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   MB_CUDA(cudaEventRecord(h->ev_end[ev], h->stream));
   h->ev_count++;
+  mark("all enqueued", chunks);
   if (ext && ext->no_sync) return 0;
   if (!c_dev && !c_pin) MB_CHECK(sg->drain());  // staged downloads reach the caller's memory here
   MB_CUDA(cudaStreamSynchronize(h->stream));
   MB_CUDA(cudaStreamSynchronize(h->copy_stream));
+  mark("streams drained", chunks);
   if (adaptive && *h_flag) {  // bound failed somewhere: exact-to-2^-62 redo, everything resident
     first_main = false;
     MB_CHECK(tc_pass(h, full, n, dB, ldB, dC, ldC, 8, 1, nullptr, nullptr, &first_main, ev));
