@@ -44,6 +44,19 @@ cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t stream) {
       uint64_t keep = 4ull << 30;
       if (const char *env = getenv("MB200_POOL_KEEP_GB")) keep = (uint64_t)(atof(env) * 1073741824.0);
       cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+      // pool memory is private to its device unless access is granted: the multi-device paths read
+      // each other's scratch (packed input of the crossproduct) over NVLink
+      int count = 0;
+      cudaGetDeviceCount(&count);
+      for (int peer = 0; peer < count; peer++) {
+        int can = 0;
+        if (peer == dev || cudaDeviceCanAccessPeer(&can, peer, dev) != cudaSuccess || !can) continue;
+        cudaMemAccessDesc desc = {};
+        desc.location.type = cudaMemLocationTypeDevice;
+        desc.location.id = peer;
+        desc.flags = cudaMemAccessFlagsProtReadWrite;
+        if (cudaMemPoolSetAccess(pools[dev], &desc, 1) != cudaSuccess) cudaGetLastError();
+      }
     }
     pool = pools[dev];
   }

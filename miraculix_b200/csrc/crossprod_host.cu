@@ -101,7 +101,7 @@ struct DevCtx {
     for (BandPlan &p : plans) crossprod_band_plan_free(&p, s_main);
     if (s_main) cudaStreamSynchronize(s_main);
     if (s_copy) cudaStreamSynchronize(s_copy);
-    cudaFree(d_x);
+    if (d_x) cudaFreeAsync(d_x, s_main);
     if (d_f) cudaFreeAsync(d_f, s_main);
     if (d_m) cudaFreeAsync(d_m, s_main);
     if (C32) cudaFreeAsync(C32, s_main);
@@ -220,14 +220,17 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     DevCtx &c = ctx[g];
     c.device = devs[g];
     MB_CUDA(cudaSetDevice(c.device));
-    for (int p = 0; p < N; p++) {  // peer access for the gather of the packed input
-      if (devs[p] == c.device) continue;
+    for (int p = 0; p < N; p++) {  // peer access for the gather of the packed input, once per pair
+      static std::atomic<unsigned long long> enabled[64];
+      const int a = c.device, b = devs[p];
+      if (a == b || a < 0 || a >= 64 || b < 0 || b >= 64 || (enabled[a].load() >> b & 1ull)) continue;
       int can = 0;
-      MB_CUDA(cudaDeviceCanAccessPeer(&can, c.device, devs[p]));
+      MB_CUDA(cudaDeviceCanAccessPeer(&can, a, b));
       if (can) {
-        const cudaError_t e = cudaDeviceEnablePeerAccess(devs[p], 0);
+        const cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
         if (e != cudaSuccess) cudaGetLastError();  // already enabled, or copies fall back to staging
       }
+      enabled[a].fetch_or(1ull << b);
     }
     MB_CUDA(cudaStreamCreateWithFlags(&c.s_main, cudaStreamNonBlocking));
     MB_CUDA(cudaStreamCreateWithFlags(&c.s_copy, cudaStreamNonBlocking));
@@ -240,8 +243,8 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     MB_CUDA(cudaEventCreate(&c.t1));
     if (!ans_pin || !x_pin) MB_CHECK(c.stager.init(4u << 20));
     // scratch from the library's pool (cached between calls: a GBLUP script calls this repeatedly)
-    // the packed matrix is read by the peers: plain cudaMalloc (pool memory is private to its device)
-    MB_CUDA(cudaMalloc(&c.d_x, (size_t)rows * nb));
+    // the packed matrix is read by the peers (the library pool grants them access, abi.cu)
+    MB_CUDA(pool_alloc(&c.d_x, (size_t)rows * nb, c.s_main));
     MB_CUDA(pool_alloc(&c.C32, sizeof(int32_t) * (size_t)acc_rows * rows_pad, c.s_main));
     for (int b = 0; b < 2; b++) {
       MB_CUDA(pool_alloc(&c.P[b], sizeof(double) * (size_t)chunk_rows * rows, c.s_main));

@@ -123,25 +123,37 @@ struct PeerSet {
 };
 
 // out[r + c rows] = sum_p part_p[r0 + r + c ld]  (p = 0..n-1 in order), amaxC[c] = max_r |out|,
-// errsum[c] = sum_p err_p[c]
+// errsum[c] = sum_p err_p[c].  blockIdx.y = column; one atomicMax per block (a per-element atomic on
+// ncols addresses serialised the kernel: 325 us for 500k elements in the first ncu capture).
 __global__ void __launch_bounds__(256)
 reduce_partials_kernel(const PeerSet ps, long ld, long r0, long rows, int ncols,
                        double *__restrict__ out, unsigned long long *__restrict__ amaxC,
                        double *__restrict__ errsum) {
-  const long total = rows * ncols;
-  for (long idx = (long)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (long)gridDim.x * 256) {
-    const long r = idx % rows;
-    const int c = (int)(idx / rows);
+  const int c = blockIdx.y;
+  double mx = 0.0;
+  bool bad = false;
+  for (long r = (long)blockIdx.x * 256 + threadIdx.x; r < rows; r += (long)gridDim.x * 256) {
     double s = 0.0;
     for (int p = 0; p < ps.n; p++) s += ps.ptr[p][r0 + r + (size_t)c * ld];
-    out[idx] = s;
-    // non-negative doubles order like their bit patterns; NaN sorts above everything (kept visible)
-    atomicMax(&amaxC[c], (unsigned long long)__double_as_longlong(fabs(s)));
+    out[r + (size_t)c * rows] = s;
+    const double a = fabs(s);
+    mx = fmax(mx, a);
+    bad |= !(a <= 1.7976931348623157e308);
   }
-  if (blockIdx.x == 0 && threadIdx.x < ncols && errsum) {
-    double e = 0.0;
-    for (int p = 0; p < ps.n; p++) e += ps.err[p] ? ps.err[p][threadIdx.x] : 0.0;
-    errsum[threadIdx.x] = e;
+  for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (__any_sync(0xffffffffu, bad)) mx = __longlong_as_double(0x7ff8000000000000ll);  // NaN stays visible
+  __shared__ unsigned long long red[8];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = (unsigned long long)__double_as_longlong(mx);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long m = 0;
+    for (int i = 0; i < 8; i++) m = red[i] > m ? red[i] : m;  // non-negative doubles order like their bits
+    atomicMax(&amaxC[c], m);
+    if (blockIdx.x == 0 && errsum) {
+      double e = 0.0;
+      for (int p = 0; p < ps.n; p++) e += ps.err[p] ? ps.err[p][c] : 0.0;
+      errsum[c] = e;
+    }
   }
 }
 
@@ -388,9 +400,10 @@ static int dgemm_n_pass(MultiHandle *m, int g, int n, const double *B, long ldb,
   pc.mark("'N' exchange point passed");
   const long rows = m->i_count[g];
   if (rows > 0) {
-    long blocks = ceil_div(rows * n, 256);
-    if (blocks > 4L * h->sm_count) blocks = 4L * h->sm_count;
-    reduce_partials_kernel<<<(unsigned)blocks, 256, 0, h->stream>>>(
+    long blocks = ceil_div(rows, 256);
+    const long cap = ceil_div(4L * h->sm_count, n);
+    if (blocks > cap) blocks = cap;
+    reduce_partials_kernel<<<dim3((unsigned)blocks, (unsigned)n), 256, 0, h->stream>>>(
         partial_set(m), m->indiv, m->i_begin[g], rows, n, m->d_red[g], m->d_chk[g],
         reinterpret_cast<double *>(m->d_chk[g] + m->max_n));
     count_launch();

@@ -45,8 +45,11 @@ class CopyPool {
     return pool;
   }
   int helpers() const { return (int)threads_.size(); }
-  void run(CopyJob &job) {
-    std::lock_guard<std::mutex> call(call_mu_);  // one 2-D copy at a time uses the helpers
+  // false: the helpers are busy with another caller's copy (several device workers stage at the
+  // same time) -- the caller then copies inline, which is the parallelism wanted in that case
+  bool run(CopyJob &job) {
+    std::unique_lock<std::mutex> call(call_mu_, std::try_to_lock);
+    if (!call.owns_lock()) return false;
     {
       std::lock_guard<std::mutex> lk(mu_);
       job_ = &job;
@@ -58,6 +61,7 @@ class CopyPool {
     std::unique_lock<std::mutex> lk(mu_);
     done_cv_.wait(lk, [&] { return job.done.load() == job.pieces && active_ == 0; });
     job_ = nullptr;
+    return true;
   }
 
  private:
@@ -145,7 +149,11 @@ void parallel_copy_2d(void *dst, size_t dpitch, const void *src, size_t spitch, 
   if (pieces > 4 * parts) pieces = 4 * parts;
   job.piece_bytes = ((total + pieces - 1) / pieces + 63) & ~(size_t)63;
   job.pieces = (total + job.piece_bytes - 1) / job.piece_bytes;
-  pool.run(job);
+  if (!pool.run(job)) {
+    job.pieces = 1;
+    job.piece_bytes = total;
+    copy_piece(job, 0);
+  }
 }
 
 bool host_is_pinned(const void *p) {

@@ -303,3 +303,116 @@ def test_k_split_tail_matches_unsplit(gpu_lib, monkeypatch):
     assert np.array_equal(panel, panel0)
     want = cport.grm_epilogue(exact_counts(Z), f, True)
     assert relerr(G, want) <= TOL
+
+
+def _device_rows(ptr, pitch, rows):
+    """Rows of a library-owned packed device matrix as a (len(rows), pitch) uint8 numpy array."""
+    import torch
+
+    class _H:
+        pass
+    out = np.empty((len(rows), pitch), dtype=np.uint8)
+    for t, r in enumerate(rows):
+        hold = _H()
+        hold.__cuda_array_interface__ = {"shape": (pitch,), "typestr": "|u1", "data": (int(ptr) + int(r) * pitch, False),
+                                         "version": 3, "strides": None}
+        out[t] = torch.as_tensor(hold, device="cuda").cpu().numpy()
+    return out
+
+
+def test_grm_partition_full_size_sampled_parity(gpu_lib):
+    """BASELINE configs[4] at FULL size: one partition (3 of 8) of the centred+scaled GRM of 1M SNPs x
+    100k individuals -- K slabs, int32 partial panel, CTA pairs with dead halves, all at once.  32
+    sampled panel entries against direct int64 dot products of the decoded packed rows and the update
+    of crossproduct.jl:91-106 in long double, with the row sums m = Z (Z^T 1) obtained independently
+    through dgemm_compressed (not centred; integer-exact).  Skips without ~120 GB of free HBM."""
+    import ctypes as C
+    import torch
+    from miraculix_b200 import api
+    snps, indiv, part, nparts = 1_000_000, 100_000, 3, 8
+    free_b, _ = torch.cuda.mem_get_info()
+    if free_b < 120e9:
+        pytest.skip("needs ~120 GB of free device memory")
+    h = api.simulate_compressed(snps, indiv, 20261105, 1)
+    try:
+        lay = api.get_layout(h)
+        pitch = lay.pitch_indiv_major
+        kcols = pitch * 4
+        f = api.get_compressed_freq(h, snps)
+        d_f = torch.zeros(kcols, dtype=torch.float64, device="cuda")
+        d_f[:snps] = torch.from_numpy(f).cuda()
+        lrows = gpu_lib.mb200_crossprod_partition_rows(indiv, part, nparts)
+        panel = torch.empty(lrows * indiv, dtype=torch.float64, device="cuda")
+        api._check(gpu_lib.mb200_crossprod_partition_device(lay.d_indiv_major, kcols, indiv, 0, 1, d_f.data_ptr(), 1,
+                                                            part, nparts, panel.data_ptr()), "partition")
+        torch.cuda.synchronize()
+        P = panel.view(lrows, indiv)
+        # exact row sums through the other kernel family
+        api.set_options(use_gpu=True, not_center=True)
+        colsum = api.dgemm_compressed("T", h, np.ones((indiv, 1)), snps, indiv)
+        m = api.dgemm_compressed("N", h, colsum, snps, indiv)[:, 0]
+        total, c = np.longdouble(m.sum()), np.longdouble(2.0 * (f * (1.0 - f)).sum())
+        rng = np.random.default_rng(4)
+        lr = rng.integers(0, lrows, size=32)
+        gi = ((lr // 128) * nparts + part) * 128 + lr % 128
+        lr, gi = lr[gi < indiv], gi[gi < indiv]
+        first = gi // 256 * 256
+        jj = first + (rng.random(gi.size) * (indiv - first)).astype(np.int64)
+        jj[0] = gi[0]                                   # a diagonal entry
+        jj[1] = indiv - 1
+        shifts = np.arange(4, dtype=np.uint8) * 2
+        Zi = _device_rows(lay.d_indiv_major, pitch, gi)
+        Zj = _device_rows(lay.d_indiv_major, pitch, jj)
+        got = P[torch.as_tensor(lr, device="cuda"), torch.as_tensor(jj, device="cuda")].cpu().numpy()
+        worst = 0.0
+        for t in range(gi.size):
+            zi = ((Zi[t][:, None] >> shifts) & 3).reshape(-1).astype(np.int64)
+            zj = ((Zj[t][:, None] >> shifts) & 3).reshape(-1).astype(np.int64)
+            cnt = np.longdouble(int(zi @ zj))
+            want = (cnt - (np.longdouble(m[gi[t]]) + np.longdouble(m[jj[t]])) / indiv + total / indiv / indiv) / c
+            worst = max(worst, abs(float(got[t] - want)))
+        assert worst <= TOL * float(np.abs(got).max()), worst
+    finally:
+        api.set_options(use_gpu=True, not_center=False)
+        api.free_compressed(h)
+
+
+def test_snp_multiply_out_of_core_large(gpu_lib):
+    """snp_multiply_gpu with more individuals than the in-core path could hold next to its int8 slab
+    and int32 matrix in one piece: 120k individuals (115 GB of fp64 result, in HOST memory only), device
+    memory bounded by TILE_SIZE.  Sampled entries, both triangles, against int64 dot products.  Skips
+    without ~150 GB of free host memory."""
+    import ctypes as C
+    import os
+    from miraculix_b200 import api
+    indiv, snps = 120_000, 4096
+    need = 8 * indiv * indiv
+    avail = 0
+    for ln in open("/proc/meminfo"):
+        if ln.startswith("MemAvailable:"):
+            avail = int(ln.split()[1]) * 1024
+    if avail < 1.3 * need:
+        pytest.skip("needs ~150 GB of free host memory")
+    rng = np.random.default_rng(6)
+    x = rng.integers(0, 256, size=(indiv, snps // 4), dtype=np.uint8)
+    x &= rng.integers(0, 256, size=(indiv, snps // 4), dtype=np.uint8)   # thin out: more zeros
+    x[(x & 0x03) == 0x03] &= 0xFE                                         # field value 3 -> 2 (values are 0..2)
+    x[(x & 0x0C) == 0x0C] &= 0xFB
+    x[(x & 0x30) == 0x30] &= 0xEF
+    x[(x & 0xC0) == 0xC0] &= 0xBF
+    M = np.empty((indiv, indiv))
+    os.environ["TILE_SIZE"] = "8192"
+    try:
+        rc = gpu_lib.snp_multiply_gpu(x.ctypes.data, snps, indiv, M.ctypes.data, False)
+    finally:
+        os.environ.pop("TILE_SIZE", None)
+    assert rc == 0, gpu_lib.mb200_last_message()
+    shifts = np.arange(4, dtype=np.uint8) * 2
+    ii = rng.integers(0, indiv, size=48)
+    jj = rng.integers(0, indiv, size=48)
+    ii[:3], jj[:3] = (0, indiv - 1, 777), (indiv - 1, indiv - 1, 777)
+    for i, j in zip(ii.tolist(), jj.tolist()):
+        zi = ((x[i][:, None] >> shifts) & 3).reshape(-1).astype(np.int64)
+        zj = ((x[j][:, None] >> shifts) & 3).reshape(-1).astype(np.int64)
+        want = float(zi @ zj)
+        assert M[i, j] == want and M[j, i] == want, (i, j)

@@ -173,3 +173,30 @@ def test_cg_two_snp_shards_with_allreduce_hook(gpu_lib):
     finally:
         for hh in handles:
             api.free_compressed(hh)
+
+
+def test_cg_full_size_residual_matches_independent_products(gpu_lib):
+    """BASELINE configs[3] at FULL size (500k SNPs x 200k individuals, device-simulated): after 5
+    iterations the solver's own ||r|| must equal ||b - (Zc Zc^T + lambda I) x|| recomputed from the
+    returned iterate through two independent dgemm_compressed calls (8-digit path) to 1e-8 of ||b||.
+    Skips without ~70 GB of free HBM."""
+    import torch
+    from miraculix_b200 import api
+    snps, indiv = 500_000, 200_000
+    free_b, _ = torch.cuda.mem_get_info()
+    if free_b < 70e9:
+        pytest.skip("needs ~70 GB of free device memory")
+    h = api.simulate_compressed(snps, indiv, 3000, 1)
+    try:
+        rng = np.random.default_rng(12)
+        b, x0 = rng.standard_normal(indiv), np.zeros(indiv)
+        lam = 0.05 * snps
+        x, it, res = api.cg_solve(h, b, x0, lam=lam, tol=0.0, max_iter=5)
+        assert it == 5
+        t = api.dgemm_compressed("T", h, x.reshape(-1, 1), snps, indiv)
+        Gx = api.dgemm_compressed("N", h, t, snps, indiv)[:, 0]
+        r = b - (Gx + lam * x)
+        assert abs(np.linalg.norm(r) - res) <= 1e-8 * np.linalg.norm(b), (np.linalg.norm(r), res)
+        assert res < 1e-2 * np.linalg.norm(b)          # it did converge on the way
+    finally:
+        api.free_compressed(h)
