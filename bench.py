@@ -324,6 +324,12 @@ def run_ours(args):
     small = None
     if rank == 0 and not args.no_small:
         small = run_small(lib, api)
+    wide = None
+    if rank == 0 and world == 1 and args.wide_ncol > 0 and not args.no_small:
+        try:
+            wide = run_wide(args, lib, api, dev)
+        except Exception as exc:
+            wide = {"error": repr(exc)}
     host_barrier()
     pcg = None
     if not args.no_pcg:
@@ -397,6 +403,8 @@ def run_ours(args):
 
     if small is not None:
         line["small"] = small
+    if wide is not None:
+        line["wide_b"] = wide
     if pcg is not None:
         line["pcg"] = pcg
     if not args.no_grm and world == 1:
@@ -550,6 +558,55 @@ def run_e2e(args, lib, api, handle, devices, seed, hBn, hBt, Cn_dev, Ct_dev, ste
             "parity": {"n_vs_device_arm": par_n, "t_vs_device_arm": par_t, "pageable_vs_pinned": par_p,
                        "ok": bool(par_n <= 1e-10 and par_t <= 1e-10 and par_p <= 1e-10),
                        "bar": "max|dC|/max|C| <= 1e-10"}}
+
+
+def run_wide(args, lib, api, dev):
+    """dgemm_compressed with B wider than one MMA's digit rows (examples/gblup/calculate_gblup.jl:89-93
+    calls with n + p = 50 columns): device-resident 'n' + 't' on the configs[2] matrix.  The column
+    groups run in one launch and share the packed tiles in L2; DRAM should see the matrix once."""
+    import torch
+    snps, indiv, ncol = args.snps, args.indiv, args.wide_ncol
+    h = api.simulate_compressed(snps, indiv, 1000, ncol)
+    g = torch.Generator(device=dev)
+    g.manual_seed(3)
+    Bn = torch.randn((ncol, snps), dtype=torch.float64, device=dev, generator=g)
+    Bt = torch.randn((ncol, indiv), dtype=torch.float64, device=dev, generator=g)
+    Cn = torch.empty((ncol, indiv), dtype=torch.float64, device=dev)
+    Ct = torch.empty((ncol, snps), dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+
+    def step():
+        api._check(lib.mb200_dgemm_compressed_device(0, h, ncol, C.c_void_p(Bn.data_ptr()), snps,
+                                                     C.c_void_p(Cn.data_ptr()), indiv), "dgemm n")
+        api._check(lib.mb200_dgemm_compressed_device(1, h, ncol, C.c_void_p(Bt.data_ptr()), indiv,
+                                                     C.c_void_p(Ct.data_ptr()), snps), "dgemm t")
+    reps = 5
+    for _ in range(2):
+        step()
+    lib.mb200_sync(h)
+    ms_arr, tr_arr = (C.c_float * (2 * reps))(), (C.c_int * (2 * reps))()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        step()
+    lib.mb200_sync(h)
+    sec = (time.perf_counter() - t0) / reps
+    got = lib.mb200_dgemm_kernel_times(h, 2 * reps, ms_arr, tr_arr)
+    k_ms = sum(ms_arr[i] for i in range(got)) / max(1, got)
+    sl = C.c_int(0)
+    lib.mb200_dgemm_last_precision(h, C.byref(sl))
+    lib.free_compressed(C.byref(h))
+    del Bn, Bt, Cn, Ct
+    torch.cuda.empty_cache()
+    hbm, _b, _s = peaks()
+    alg = (dgemm_bytes(indiv, snps, ncol) + dgemm_bytes(snps, indiv, ncol)) / 2
+    groups = -(-ncol // (80 // max(1, sl.value)))
+    return {"workload": f"dgemm_compressed 'n'+'t', ncol={ncol}, {snps} SNPs x {indiv} individuals, device-resident",
+            "ms_per_step": sec * 1e3, "main_kernel_ms": k_ms, "digits": sl.value, "column_groups": groups,
+            "value": 2.0 * snps * indiv * ncol / sec, "unit": UNIT,
+            "roofline": {"bound": "hbm", "achieved": alg / (k_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": alg / (k_ms * 1e-3) / 1e9 / hbm,
+                         "note": "algorithmic bytes = the packed matrix ONCE + B + C; the launch does "
+                                 f"{groups}x the tensor work of a {80 // max(1, sl.value)}-column call"}}
 
 
 def run_small(lib, api):
@@ -744,6 +801,8 @@ def grm_e2e(lib, api, hx, kcols, indiv, hf, devices, pinned, reps, parity=None):
     if pinned:
         hans_t = torch.empty(indiv * indiv, dtype=torch.float64).pin_memory()
         hans = hans_t.numpy().reshape(indiv, indiv)
+        hx_t = torch.from_numpy(hx).pin_memory()          # the packed input is page-locked too
+        hx = hx_t.numpy()
     else:
         hans = np.empty((indiv, indiv))
         hans.fill(0.0)                                   # first touch outside the timed region

@@ -273,6 +273,7 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
       MB_CUDA(cudaMemcpyAsync(c.d_x + xr0[p] * nb, ctx[p].d_x + xr0[p] * nb, (size_t)(xr0[p + 1] - xr0[p]) * nb,
                               cudaMemcpyDefault, c.s_main));
     }
+    if (g == 0) debug_info("  input upload + peer gather enqueued at %.2f ms", since());
     MB_CUDA(cudaEventRecord(c.t0, c.s_main));
     if (mode == 1) MB_CHECK(crossprod_row_sums(c.d_x, k, rows, is_plink, c.d_f, do_scale, c.d_m, c.s_main));
     // 2./3. my bands
@@ -283,6 +284,7 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
       const int tb = band_begin[b], te = band_begin[b + 1];
       const long b0 = (long)tb * 128, b1 = (long)te * 128 < rows ? (long)te * 128 : rows;
       MB_CHECK(crossprod_band_counts(c.d_x, k, rows, is_plink, c.plans[pi], c.C32, c.s_main, &c.ops));
+      if (g == 0) debug_info("  band %d [%d, %d) GEMM enqueued at %.2f ms", b, tb, te, since());
       for (long c0 = b0; c0 < b1; c0 += chunk_rows, buf ^= 1) {
         const long crows = b1 - c0 < chunk_rows ? b1 - c0 : chunk_rows;  // real rows (the last may be ragged)
         const long w = rows - c0;

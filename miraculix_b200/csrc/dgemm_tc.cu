@@ -178,7 +178,11 @@ struct DtParams {
   int R;                // groups per CTA (3 or 4)
   int row_blocks;       // ceil(rows / (128 R))
   int ksplits, cps;     // K splits and chunks per split
-  int N, S, ncols;      // MMA N (multiple of 16), digits per column, columns this pass
+  int N, S, ncols;      // MMA N (multiple of 16), digits per column, ALL columns of the launch
+  int cgroups, cpg;     // column groups of cpg columns each (<= N / S): a unit works on ONE group;
+                        // units of the same (row block, K split) are consecutive in the work list,
+                        // so the groups' CTAs read the same packed tiles at the same time (L2 hits:
+                        // B wider than one group no longer re-streams the matrix from HBM)
   double *C;            // centre-initialised output, column-major
   long ldc;
   const int *exps;      // e_c per column
@@ -200,18 +204,20 @@ __device__ long long g_dt_trace[32];
 // The CTA's work list as a stream of K chunks: unit u = blockIdx.x + i gridDim.x covers chunks
 // [c0, c1) of row block rb.  Every role walks the same stream with its own cursor.
 struct DtCursor {
-  int u, rb, kc, c1;
+  int u, rb, kc, c1, cg;
   bool first;  // kc is the first chunk of its unit
   __device__ __forceinline__ void open(const DtParams &p, int unit) {
     u = unit;
-    rb = u % p.row_blocks;
-    const int ks = u / p.row_blocks;
+    cg = u % p.cgroups;
+    const int v = u / p.cgroups;
+    rb = v % p.row_blocks;
+    const int ks = v / p.row_blocks;
     kc = ks * p.cps;
     c1 = min(kc + p.cps, p.nchunks);
     first = true;
   }
   __device__ __forceinline__ bool valid(const DtParams &p) const {
-    return u < p.row_blocks * p.ksplits;
+    return u < p.row_blocks * p.ksplits * p.cgroups;
   }
   __device__ __forceinline__ bool last() const { return kc + 1 == c1; }
   __device__ __forceinline__ void next(const DtParams &p, int stride) {
@@ -284,8 +290,9 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
         if (elect_one()) {
           const int k0 = c.kc * 512 + half * 256;
           mbar_expect_tx(&b_full[bs], (uint32_t)bslot_bytes);
-          tma_load_2d(bring + bs * bslot_bytes, &tmap_b, &b_full[bs], k0, 0);
-          tma_load_2d(bring + bs * bslot_bytes + sub_bytes, &tmap_b, &b_full[bs], k0 + 128, 0);
+          const int drow = c.cg * p.cpg * p.S;  // first digit row of this unit's column group
+          tma_load_2d(bring + bs * bslot_bytes, &tmap_b, &b_full[bs], k0, drow);
+          tma_load_2d(bring + bs * bslot_bytes + sub_bytes, &tmap_b, &b_full[bs], k0 + 128, drow);
         }
         __syncwarp();
         if (++bs == DT_BSLOTS) { bs = 0; bph ^= 1; }
@@ -490,7 +497,9 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
           tc_fence_after();
           DT_SEG(6)
           const long row = ((long)c.rb * R + g) * 128 + r;
-          for (int col = 0; col < p.ncols; col++) {
+          const int col0 = c.cg * p.cpg;
+          const int ncg = min(p.cpg, p.ncols - col0);
+          for (int col = 0; col < ncg; col++) {
             uint32_t d[8];
             tmem_ld_32x32b_x8(lane_base + g * p.N + col * p.S, d);
             tmem_ld_wait();
@@ -502,9 +511,9 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
             for (int j = 4; j < 8; j++)
               if (j < p.S) hi += (long long)(int)d[j] << (8 * (j - 4));
             const double val = fma((double)hi, 4294967296.0, (double)lo);
-            const int ex = p.exps[col];
+            const int ex = p.exps[col0 + col];
             if (row < p.rows)
-              atomicAdd(&p.C[row + (size_t)col * p.ldc],
+              atomicAdd(&p.C[row + (size_t)(col0 + col) * p.ldc],
                         ex == DT_BAD_EXP ? __longlong_as_double(0x7ff8000000000000ll) : scalbn(val, ex - P));
           }
           tc_fence_before();
@@ -530,7 +539,8 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
 // ---------------------------------------------------------------------------------------------
 static int ensure_bq(Handle *h) {
   const long kp = (h->pitch_s > h->pitch_i ? h->pitch_s : h->pitch_i) * 4;  // K pitch in int8
-  const size_t need = (size_t)DT_NMAX * kp;
+  // digit rows of ALL columns (8 digits at most) plus one MMA box of slack for the last group
+  const size_t need = ((size_t)round_up((long)h->max_n * 8, 16) + DT_NMAX) * kp;
   if (h->d_Bq && h->bq_bytes >= need) return 0;
   if (h->d_Bq) MB_CUDA(cudaFree(h->d_Bq));
   h->d_Bq = nullptr;
@@ -661,50 +671,54 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
   CUtensorMap tz;
   MB_CHECK(make_tmap_u8_2d(&tz, v.Z, row_bytes, rows, v.pitch, 128, 128, 1));
 
-  const int cpp = DT_NMAX / S;  // columns per pass
-  for (int c0 = 0; c0 < n; c0 += cpp) {
-    const int nc = n - c0 < cpp ? n - c0 : cpp;
-    const int N = (int)round_up((long)nc * S, 16);
-    const double *B = dB + (size_t)c0 * ldb;
-    quantize_kernel<<<(unsigned)ceil_div(K, 256), 256, 0, h->stream>>>(
-        B, ldb, K, nc, S, sc.amaxB + c0, h->d_Bq, kpitch, sc.exps + c0, guard);
-    count_launch();
-    MB_LAUNCH_CHECK();
-
-    CUtensorMap tb;
-    MB_CHECK(make_tmap_u8_2d(&tb, h->d_Bq, row_bytes * 4, N, kpitch, 128, N, 1));
-    DtParams p;
-    p.rows = rows;
-    p.nchunks = (int)(row_bytes / 128);
-    p.R = dt_groups(N);
-    p.row_blocks = (int)ceil_div(rows, p.R * 128);
-    long ksplits = ceil_div(20L * h->sm_count, p.row_blocks);
-    if (ksplits > p.nchunks / 8) ksplits = p.nchunks / 8;
-    if (ksplits < 1) ksplits = 1;
-    if (ksplits < ceil_div(p.nchunks, 128)) ksplits = ceil_div(p.nchunks, 128);  // int32 headroom:
-    p.cps = (int)ceil_div(p.nchunks, ksplits);  // 65536 K x (128 x 128) per term < 2^31
-    p.ksplits = (int)ceil_div(p.nchunks, p.cps);
-    p.N = N;
-    p.S = S;
-    p.ncols = nc;
-    p.C = dC + (size_t)c0 * ldc;
-    p.ldc = ldc;
-    p.exps = sc.exps + c0;
-    p.guard = guard;
-    p.flags = env.flags;
-    p.dbg = env.trace ? env.dbg : 0;
-    const long units = (long)p.row_blocks * p.ksplits;
-    const int grid = (int)(units < h->sm_count ? units : h->sm_count);
-    if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
-    *first_main = false;
-    MB_CHECK(tc_prepare_device(h->device));
-    void (*kern)(CUtensorMap, CUtensorMap, DtParams) = dgemm_tc_kernel<false, -1>;
-    if (env.trace) kern = dgemm_tc_kernel<true, -1>;
-    else if (env.probe >= 0) kern = dt_probe_kernel(env.probe);
-    kern<<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
-    count_launch();
-    MB_LAUNCH_CHECK();
-  }
+  // Column groups of cpg <= DT_NMAX / S columns (the MMA's N rows of digits); all groups run in ONE
+  // launch, their units interleaved so that the groups of one (row block, K split) stream the same
+  // packed tiles at the same time: DRAM sees the matrix once however wide B is.
+  const int cpg_max = DT_NMAX / S;
+  const int cgroups = (int)ceil_div(n, cpg_max);
+  const int cpg = (int)ceil_div(n, cgroups);  // balanced: 50 columns at S = 6 -> 4 groups of 13, 13, 13, 11
+  const int N = (int)round_up((long)cpg * S, 16);
+  quantize_kernel<<<(unsigned)ceil_div(K, 256), 256, 0, h->stream>>>(dB, ldb, K, n, S, sc.amaxB, h->d_Bq, kpitch,
+                                                                    sc.exps, guard);
+  count_launch();
+  MB_LAUNCH_CHECK();
+  // digit rows of the whole panel; the last group's box may reach past them into rows that are
+  // zero or stale digits: they feed accumulator columns nobody reads
+  CUtensorMap tb;
+  MB_CHECK(make_tmap_u8_2d(&tb, h->d_Bq, row_bytes * 4, (long)(cgroups - 1) * cpg * S + N, kpitch, 128, N, 1));
+  DtParams p;
+  p.rows = rows;
+  p.nchunks = (int)(row_bytes / 128);
+  p.R = dt_groups(N);
+  p.row_blocks = (int)ceil_div(rows, p.R * 128);
+  long ksplits = ceil_div(20L * h->sm_count, (long)p.row_blocks * cgroups);
+  if (ksplits > p.nchunks / 8) ksplits = p.nchunks / 8;
+  if (ksplits < 1) ksplits = 1;
+  if (ksplits < ceil_div(p.nchunks, 128)) ksplits = ceil_div(p.nchunks, 128);  // int32 headroom:
+  p.cps = (int)ceil_div(p.nchunks, ksplits);  // 65536 K x (128 x 128) per term < 2^31
+  p.ksplits = (int)ceil_div(p.nchunks, p.cps);
+  p.N = N;
+  p.S = S;
+  p.ncols = n;
+  p.cgroups = cgroups;
+  p.cpg = cpg;
+  p.C = dC;
+  p.ldc = ldc;
+  p.exps = sc.exps;
+  p.guard = guard;
+  p.flags = env.flags;
+  p.dbg = env.trace ? env.dbg : 0;
+  const long units = (long)p.row_blocks * p.ksplits * cgroups;
+  const int grid = (int)(units < h->sm_count ? units : h->sm_count);
+  if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
+  *first_main = false;
+  MB_CHECK(tc_prepare_device(h->device));
+  void (*kern)(CUtensorMap, CUtensorMap, DtParams) = dgemm_tc_kernel<false, -1>;
+  if (env.trace) kern = dgemm_tc_kernel<true, -1>;
+  else if (env.probe >= 0) kern = dt_probe_kernel(env.probe);
+  kern<<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+  count_launch();
+  MB_LAUNCH_CHECK();
   return 0;
 }
 

