@@ -148,6 +148,11 @@ unsigned long long mb200_kernel_launches(void);
  *   rowsum_max * 2^(e_c - 47) <= 5e-11 * max_r |C[r,c]|   for every column c
  * and recomputed with 8 digits (error <= 2^-62 relative to max|B_c|) when the bound fails. */
 int mb200_set_dgemm_mode(int mode, int slices);
+/* B wider than one group of columns (13 at 6 digits, 10 at 8): 0 (default) = the groups' work units
+ * are interleaved in one launch and share the packed tiles in L2; 1 = thread-block clusters of 2 / 4
+ * CTAs with the packed tiles multicast (DRAM sees the matrix once; slower in time on B200 because
+ * clusters of 4 occupy 132 of 148 SMs -- DESIGN.md 3.2).  Results are identical. */
+int mb200_set_dgemm_wide_cluster(int on);
 /* Host-pointer dgemm_compressed overlaps the PCIe copies of the snps x n panel (B for 'N', C for
  * 'T') with the kernels by cutting the SNP axis into `chunks` pieces (default 4, at most 16;
  * boundaries multiples of 512 SNPs), fewer when a chunk would hold less than min_bytes of that

@@ -119,6 +119,7 @@ Options &options() {
     if (const char *e = getenv("MB200_DGEMM_MODE")) v.dgemm_mode = atoi(e);
     if (const char *e = getenv("MB200_DGEMM_SLICES")) v.dgemm_slices = atoi(e);
     if (const char *e = getenv("MB200_CROSSPROD_MODE")) v.crossprod_mode = atoi(e);
+    if (const char *e = getenv("MB200_WIDE_CLUSTER")) v.wide_cluster = atoi(e) != 0;
     if (const char *e = getenv("MB200_PIPE_CHUNKS")) v.pipe_chunks = atoi(e);
     if (const char *e = getenv("MB200_PIPE_MIN_BYTES")) v.pipe_min_bytes = atof(e);
     return v;
@@ -344,6 +345,10 @@ int mb200_set_dgemm_mode(int mode, int slices) {
   Options &o = options();
   if (mode == 0 || mode == 1) o.dgemm_mode = mode;
   if (slices == 0 || (slices >= 3 && slices <= 8)) o.dgemm_slices = slices;
+  return 0;
+}
+int mb200_set_dgemm_wide_cluster(int on) {
+  options().wide_cluster = on ? 1 : 0;
   return 0;
 }
 int mb200_set_pipeline(int chunks, double min_bytes) {

@@ -23,6 +23,7 @@
 #include <cuda.h>
 #include <math.h>
 #include <chrono>
+#include <mutex>
 #include <stdlib.h>
 #include "common.cuh"
 #include "handle.h"
@@ -163,10 +164,14 @@ constexpr int DT_ZBYTES = 128 * 128;
 constexpr int DT_BSLOTS = 4;               // digit ring: 2 sub-tiles [N rows][128 B] per slot (K = 256)
 constexpr int DT_ASLOTS = 2;               // TMEM A-operand slots per group: 32 columns (K = 128) each
 constexpr int DT_THREADS = 21 * 32;
-constexpr int DT_NBAR = DT_RMAX * (DT_ZSLOTS + 2 * DT_ASLOTS + 2) + 2 * DT_BSLOTS;
+constexpr int DT_ZSLOTS_CL = 3;            // cluster (wide-B) mode: 3 groups x 3 slots; the extra slot hides the
+constexpr int DT_RMAX_CL = 3;              // cluster-wide release -> multicast refill round trip
+constexpr int DT_ZBAR = 12;                // z_full / z_empty entries reserved (>= groups x slots of both modes)
+constexpr int DT_NBAR = 2 * DT_ZBAR + DT_RMAX * (2 * DT_ASLOTS + 2) + 2 * DT_BSLOTS;
 
-__host__ __device__ constexpr int dt_smem_bytes(int N) {
-  return DT_RMAX * DT_ZSLOTS * DT_ZBYTES + DT_BSLOTS * 2 * N * 128 + 1024 /*align*/ +
+__host__ __device__ constexpr int dt_smem_bytes(int N, bool cluster = false) {
+  return (cluster ? DT_RMAX_CL * DT_ZSLOTS_CL : DT_RMAX * DT_ZSLOTS) * DT_ZBYTES + DT_BSLOTS * 2 * N * 128 +
+         1024 /*align*/ +
          8 * DT_NBAR + 16;
 }
 // groups that fit TMEM: R * N accumulator columns + R * 2 * 32 A-ring columns <= 512
@@ -205,11 +210,17 @@ __device__ long long g_dt_trace[32];
 // [c0, c1) of row block rb.  Every role walks the same stream with its own cursor.
 struct DtCursor {
   int u, rb, kc, c1, cg;
+  int fixed_cg = -1;  // cluster mode: the CTA's column group is its cluster rank, units count (rb, ks) only
   bool first;  // kc is the first chunk of its unit
   __device__ __forceinline__ void open(const DtParams &p, int unit) {
     u = unit;
-    cg = u % p.cgroups;
-    const int v = u / p.cgroups;
+    int v = u;
+    if (fixed_cg >= 0) {
+      cg = fixed_cg;
+    } else {
+      cg = u % p.cgroups;
+      v = u / p.cgroups;
+    }
     rb = v % p.row_blocks;
     const int ks = v / p.row_blocks;
     kc = ks * p.cps;
@@ -217,7 +228,7 @@ struct DtCursor {
     first = true;
   }
   __device__ __forceinline__ bool valid(const DtParams &p) const {
-    return u < p.row_blocks * p.ksplits * p.cgroups;
+    return u < p.row_blocks * p.ksplits * (fixed_cg >= 0 ? 1 : p.cgroups);
   }
   __device__ __forceinline__ bool last() const { return kc + 1 == c1; }
   __device__ __forceinline__ void next(const DtParams &p, int stride) {
@@ -236,8 +247,14 @@ __device__ __forceinline__ void group_bar_sync(int g) {  // named barrier 1 + g,
 // stored).  Results are garbage; timing only.  PROBE < 0: the product kernel (TRACE: p.dbg bits).
 // PROBE == 8: an encoding experiment with CORRECT results -- the A operand carries the genotype
 // itself (0/1/2, right shifts) instead of 64 x genotype (left shifts).
-template <bool TRACE, int PROBE>
-__global__ void __launch_bounds__(DT_THREADS, 1)
+//
+// CL > 1 (wide B, 2 or 4 column groups): a thread-block cluster of CL CTAs works on ONE (row block,
+// K split); CTA rank r owns column group r.  The packed-Z tiles are the same for all of them: a
+// 22nd warp in every CTA loads 1 / CL of each tile and MULTICASTS it to the cluster, so the matrix
+// leaves DRAM and L2 once however wide B is.  A slot may be refilled when every CTA of the cluster
+// has read it: the groups release it with remote arrives on z_empty (count CL) in all CTAs.
+template <bool TRACE, int PROBE, int CL>
+__global__ void __launch_bounds__(CL > 1 ? DT_THREADS + 32 : DT_THREADS, 1)
 dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
                 const __grid_constant__ CUtensorMap tmap_b, const DtParams p) {
   if (p.guard && *p.guard == 0) return;  // uniform over the grid
@@ -245,25 +262,32 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                               ~(uintptr_t)1023);
   uint8_t *zring = smem;                                         // [group][slot][128][128 B]
-  uint8_t *bring = smem + DT_RMAX * DT_ZSLOTS * DT_ZBYTES;
+  constexpr int ZS = CL > 1 ? DT_ZSLOTS_CL : DT_ZSLOTS;  // packed-Z slots per group
+  uint8_t *bring = smem + (CL > 1 ? DT_RMAX_CL * DT_ZSLOTS_CL : DT_RMAX * DT_ZSLOTS) * DT_ZBYTES;
   const int sub_bytes = p.N * 128;          // one digit sub-tile: N rows x 128 K-bytes
   const int bslot_bytes = 2 * sub_bytes;    // half a K chunk: 256
   uint64_t *bars = reinterpret_cast<uint64_t *>(bring + DT_BSLOTS * bslot_bytes);
-  uint64_t *z_full = bars;                                   // [g][DT_ZSLOTS]
-  uint64_t *a_full = z_full + DT_RMAX * DT_ZSLOTS;           // [g][DT_ASLOTS]
+  uint64_t *z_full = bars;                                   // [g][ZS]
+  uint64_t *a_full = z_full + DT_ZBAR;                       // [g][DT_ASLOTS]
   uint64_t *a_empty = a_full + DT_RMAX * DT_ASLOTS;          // [g][DT_ASLOTS]
   uint64_t *d_full = a_empty + DT_RMAX * DT_ASLOTS;          // [g]
   uint64_t *d_empty = d_full + DT_RMAX;                      // [g]
   uint64_t *b_full = d_empty + DT_RMAX, *b_empty = b_full + DT_BSLOTS;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(b_empty + DT_BSLOTS);
+  uint64_t *z_empty = b_empty + DT_BSLOTS;                   // [g][ZS], cluster mode only
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(z_empty + DT_ZBAR);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.R;
-  const int stride = gridDim.x;
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int stride = CL > 1 ? gridDim.x / CL : gridDim.x;
+  const int unit0 = CL > 1 ? blockIdx.x / CL : blockIdx.x;
+  const int fixed_cg = CL > 1 ? crank : -1;
   const int dbg = PROBE >= 0 ? (PROBE & 7) : (TRACE ? p.dbg : 0);
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < DT_RMAX * DT_ZSLOTS; i++) mbar_init(&z_full[i], 1);
+    for (int i = 0; i < DT_ZBAR; i++) mbar_init(&z_full[i], 1);
+    if (CL > 1)
+      for (int i = 0; i < DT_ZBAR; i++) mbar_init(&z_empty[i], CL);
     for (int i = 0; i < DT_RMAX * DT_ASLOTS; i++) { mbar_init(&a_full[i], 4); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < DT_RMAX; i++) { mbar_init(&d_full[i], 1); mbar_init(&d_empty[i], 4); }
     for (int i = 0; i < DT_BSLOTS; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], R); }
@@ -274,16 +298,38 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   if (warp == 20) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();  // the peers' barriers exist before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t acol0 = (uint32_t)(R * p.N);  // accumulators below, A slots above
 
-  if (warp == 20) {
+  if (CL > 1 && warp == 21) {
+    // ===== cluster mode: producer of the packed-Z tiles of all groups (1 / CL of each, multicast) =====
+    constexpr int QROWS = 128 / (CL > 1 ? CL : 1);
+    DtCursor c;
+    c.fixed_cg = fixed_cg;
+    uint32_t q = 0;
+    for (c.open(p, unit0); c.valid(p); c.next(p, stride), q++) {
+      const int zs = q % ZS;
+      const uint32_t par = ((q / ZS) & 1) ^ 1;
+      for (int g = 0; g < R; g++) {
+        uint64_t *ze = &z_empty[g * ZS + zs], *zfb = &z_full[g * ZS + zs];
+        mbar_wait_warp_cluster(ze, par);  // every CTA of the cluster has read the slot
+        if (elect_one()) {
+          mbar_expect_tx(zfb, DT_ZBYTES);
+          tma_load_2d_multicast(zring + (g * ZS + zs) * DT_ZBYTES + crank * (QROWS * 128), &tmap_z, zfb,
+                                c.kc * 128, (c.rb * R + g) * 128 + crank * QROWS, (uint16_t)((1u << CL) - 1));
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 20) {
     // ===== TMA producer of the digit tiles (whole warp walks, one elected lane issues) =====
     int bs = 0;
     uint32_t bph = 0;
     DtCursor c;
-    for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride)) {
+    c.fixed_cg = fixed_cg;
+    for (c.open(p, unit0); c.valid(p); c.next(p, stride)) {
 #pragma unroll
       for (int half = 0; half < 2; half++) {
         mbar_wait_warp(&b_empty[bs], bph ^ 1);
@@ -311,7 +357,8 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
       bool a_ready = false, b_ready = false;
       long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = TRACE ? clock64() : 0;
       DtCursor c;
-      for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride)) {
+      c.fixed_cg = fixed_cg;
+      for (c.open(p, unit0); c.valid(p); c.next(p, stride)) {
         if (c.first) {
           mbar_wait_warp(&d_empty[g], dph ^ 1);  // epilogue of the previous unit drained D
           tc_fence_after();
@@ -373,9 +420,9 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
       const uint32_t lane_base = tmem_base + ((uint32_t)(32 * w) << 16);
       const uint32_t a_col = acol0 + g * DT_ASLOTS * 32;
       const int P = 8 * p.S - 2 + (PROBE == 8 ? 0 : 6);  // + 6: the A operand carries 64 x genotype
-      uint8_t *zslots = zring + g * DT_ZSLOTS * DT_ZBYTES;
+      uint8_t *zslots = zring + g * ZS * DT_ZBYTES;
       const uint32_t zrow0 = smem_u32(zslots) + (uint32_t)r * 128 + (uint32_t)((r & 7) << 4);
-      uint64_t *zf = z_full + g * DT_ZSLOTS;
+      uint64_t *zf = z_full + g * ZS;
       uint64_t *af = a_full + g * DT_ASLOTS, *ae = a_empty + g * DT_ASLOTS;
       uint32_t q = 0;    // K chunks processed by this group so far
       uint32_t dph = 0;
@@ -385,8 +432,9 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
       // second cursor DT_ZSLOTS chunks ahead and refills a slot as soon as all four warps have
       // read it (named barrier), so no separate producer warp or empty-barrier is needed.
       DtCursor pc;
-      pc.open(p, blockIdx.x);
-      if (w == 0) {
+      pc.fixed_cg = fixed_cg;
+      pc.open(p, unit0);
+      if (CL == 1 && w == 0) {
 #pragma unroll
         for (int s = 0; s < DT_ZSLOTS; s++) {
           if (pc.valid(p)) {
@@ -402,9 +450,10 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
       }
 
       DtCursor c;
-      for (c.open(p, blockIdx.x); c.valid(p); c.next(p, stride), q++) {
-        const int zs = q & (DT_ZSLOTS - 1);
-        mbar_wait(&zf[zs], (q / DT_ZSLOTS) & 1);
+      c.fixed_cg = fixed_cg;
+      for (c.open(p, unit0); c.valid(p); c.next(p, stride), q++) {
+        const int zs = q % ZS;
+        mbar_wait(&zf[zs], (q / ZS) & 1);
         DT_SEG(0)
         // 128-byte swizzle: 16-byte chunk cc of row r sits at chunk index cc ^ (r & 7).  Explicit
         // shared-space loads with 32-bit addresses (the generic-pointer form compiled to LD.E.128
@@ -436,7 +485,12 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
         }
 #endif
         group_bar_sync(g);  // all 128 rows of the slot are in registers
-        if (w == 0) {
+        if (CL > 1) {
+          // cluster mode: release the slot in EVERY CTA of the cluster (their producers multicast
+          // into this CTA's copy of the slot as well)
+          if (w == 0 && lane < CL)
+            mbar_arrive_cluster(mapa_u32(smem_u32(&z_empty[g * ZS + zs]), (uint32_t)lane));
+        } else if (w == 0) {
           if (pc.valid(p)) {
             if (elect_one()) {
               mbar_expect_tx(&zf[zs], DT_ZBYTES);
@@ -528,6 +582,7 @@ dgemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_z,
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();  // peers may still multicast into this CTA / arrive on its barriers
   if (warp == 20) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -622,25 +677,62 @@ static const TcEnv &tc_env() {
 // device this process launches the kernel on (single-process multi-GPU handles, multi.cu).
 typedef void (*DtKernel)(CUtensorMap, CUtensorMap, DtParams);
 static DtKernel dt_probe_kernel(int bits) {
-  static const DtKernel k[9] = {dgemm_tc_kernel<false, 0>, dgemm_tc_kernel<false, 1>,
-                                dgemm_tc_kernel<false, 2>, dgemm_tc_kernel<false, 3>,
-                                dgemm_tc_kernel<false, 4>, dgemm_tc_kernel<false, 5>,
-                                dgemm_tc_kernel<false, 6>, dgemm_tc_kernel<false, 7>,
-                                dgemm_tc_kernel<false, 8>};
+  static const DtKernel k[9] = {dgemm_tc_kernel<false, 0, 1>, dgemm_tc_kernel<false, 1, 1>,
+                                dgemm_tc_kernel<false, 2, 1>, dgemm_tc_kernel<false, 3, 1>,
+                                dgemm_tc_kernel<false, 4, 1>, dgemm_tc_kernel<false, 5, 1>,
+                                dgemm_tc_kernel<false, 6, 1>, dgemm_tc_kernel<false, 7, 1>,
+                                dgemm_tc_kernel<false, 8, 1>};
   return k[bits < 0 || bits > 8 ? 0 : bits];
 }
 static int tc_prepare_device(int device) {
   static std::atomic<unsigned long long> done{0};
   if (device >= 0 && device < 64 && (done.load(std::memory_order_acquire) >> device & 1ull)) return 0;
-  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                dt_smem_bytes(DT_NMAX)));
-  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<true, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                dt_smem_bytes(DT_NMAX)));
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false, -1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               dt_smem_bytes(DT_NMAX, true)));
+  MB_CUDA(cudaFuncSetAttribute(dgemm_tc_kernel<false, -1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               dt_smem_bytes(DT_NMAX, true)));
   for (int b = 0; b <= 8; b++)
     MB_CUDA(cudaFuncSetAttribute(dt_probe_kernel(b), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  dt_smem_bytes(DT_NMAX)));
   if (device >= 0 && device < 64) done.fetch_or(1ull << device, std::memory_order_release);
   return 0;
+}
+
+// Clusters of CL CTAs of the wide-B kernel that are co-resident on this device (cached per device).
+static int tc_clusters(int device, int CL, int sm_count) {
+  static std::atomic<int> cache[64][2];
+  static std::once_flag once;
+  std::call_once(once, [] {
+    for (auto &d : cache)
+      for (auto &c : d) c.store(-1);
+  });
+  const int slot = CL == 2 ? 0 : 1;
+  if (device >= 0 && device < 64 && cache[device][slot].load() >= 0) return cache[device][slot].load();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(sm_count / CL * CL));
+  cfg.blockDim = dim3(DT_THREADS + 32);
+  cfg.dynamicSmemBytes = dt_smem_bytes(DT_NMAX, true);
+  cudaLaunchAttribute at;
+  at.id = cudaLaunchAttributeClusterDimension;
+  at.val.clusterDim.x = CL;
+  at.val.clusterDim.y = 1;
+  at.val.clusterDim.z = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  const cudaError_t e = CL == 2 ? cudaOccupancyMaxActiveClusters(&n, dgemm_tc_kernel<false, -1, 2>, &cfg)
+                                : cudaOccupancyMaxActiveClusters(&n, dgemm_tc_kernel<false, -1, 4>, &cfg);
+  if (e != cudaSuccess || n < 1) {
+    cudaGetLastError();
+    n = 0;
+  }
+  if (n > sm_count / CL) n = sm_count / CL;
+  if (device >= 0 && device < 64) cache[device][slot].store(n);
+  return n;
 }
 
 // One product on a view at S digits per column: centring term into C, then per column group
@@ -675,7 +767,22 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
   // launch, their units interleaved so that the groups of one (row block, K split) stream the same
   // packed tiles at the same time: DRAM sees the matrix once however wide B is.
   const int cpg_max = DT_NMAX / S;
-  const int cgroups = (int)ceil_div(n, cpg_max);
+  int cgroups = (int)ceil_div(n, cpg_max);
+  // Default: the groups' units are interleaved in one ordinary launch (they share the packed tiles
+  // in L2 as long as their CTAs stay close: DRAM reads 2.9x one pass at 50 columns, but the launch
+  // is TENSOR bound at 5x the MACs of a 10-column call, 22.0 ms, so the re-reads cost no time).
+  // Opt-in (mb200_set_dgemm_wide_cluster / MB200_WIDE_CLUSTER=1), 2..4 groups: a cluster of 2 or 4
+  // CTAs per (row block, K split) with the packed tiles MULTICAST (the kernel's CL > 1 mode): DRAM
+  // reads 1.11x one pass, L2 traffic 122 instead of 262 GB -- but clusters of 4 fit only 132 of the
+  // 148 SMs and run in lockstep: 30.3 ms (profiles/r2_wide_b.txt).
+  int CL = 1, nclusters = 0;
+  if (cgroups >= 2 && cgroups <= 4 && o.wide_cluster && !env.trace && env.probe < 0) {
+    CL = cgroups == 2 ? 2 : 4;
+    MB_CHECK(tc_prepare_device(h->device));
+    nclusters = tc_clusters(h->device, CL, h->sm_count);
+    if (nclusters >= 1) cgroups = CL;
+    else CL = 1;
+  }
   const int cpg = (int)ceil_div(n, cgroups);  // balanced: 50 columns at S = 6 -> 4 groups of 13, 13, 13, 11
   const int N = (int)round_up((long)cpg * S, 16);
   quantize_kernel<<<(unsigned)ceil_div(K, 256), 256, 0, h->stream>>>(dB, ldb, K, n, S, sc.amaxB, h->d_Bq, kpitch,
@@ -689,9 +796,10 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
   DtParams p;
   p.rows = rows;
   p.nchunks = (int)(row_bytes / 128);
-  p.R = dt_groups(N);
+  p.R = CL > 1 ? DT_RMAX_CL : dt_groups(N);  // cluster mode: 3 groups x 3 packed-Z slots
   p.row_blocks = (int)ceil_div(rows, p.R * 128);
-  long ksplits = ceil_div(20L * h->sm_count, (long)p.row_blocks * cgroups);
+  long ksplits = CL > 1 ? ceil_div(20L * nclusters, (long)p.row_blocks)
+                        : ceil_div(20L * h->sm_count, (long)p.row_blocks * cgroups);
   if (ksplits > p.nchunks / 8) ksplits = p.nchunks / 8;
   if (ksplits < 1) ksplits = 1;
   if (ksplits < ceil_div(p.nchunks, 128)) ksplits = ceil_div(p.nchunks, 128);  // int32 headroom:
@@ -708,15 +816,35 @@ static int tc_pass(Handle *h, const DgemmView &v, int n, const double *dB, long 
   p.guard = guard;
   p.flags = env.flags;
   p.dbg = env.trace ? env.dbg : 0;
-  const long units = (long)p.row_blocks * p.ksplits * cgroups;
-  const int grid = (int)(units < h->sm_count ? units : h->sm_count);
   if (*first_main) MB_CUDA(cudaEventRecord(h->ev_begin[ev], h->stream));
   *first_main = false;
   MB_CHECK(tc_prepare_device(h->device));
-  void (*kern)(CUtensorMap, CUtensorMap, DtParams) = dgemm_tc_kernel<false, -1>;
-  if (env.trace) kern = dgemm_tc_kernel<true, -1>;
-  else if (env.probe >= 0) kern = dt_probe_kernel(env.probe);
-  kern<<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+  if (CL > 1) {
+    CUtensorMap tzq;  // 1 / CL of a packed tile per CTA, multicast to the cluster
+    MB_CHECK(make_tmap_u8_2d(&tzq, v.Z, row_bytes, rows, v.pitch, 128, 128 / CL, 1));
+    const long units = (long)p.row_blocks * p.ksplits;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((units < nclusters ? units : nclusters) * CL));
+    cfg.blockDim = dim3(DT_THREADS + 32);
+    cfg.dynamicSmemBytes = dt_smem_bytes(N, true);
+    cfg.stream = h->stream;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = CL;
+    at.val.clusterDim.y = 1;
+    at.val.clusterDim.z = 1;
+    cfg.attrs = &at;
+    cfg.numAttrs = 1;
+    if (CL == 2) MB_CUDA(cudaLaunchKernelEx(&cfg, dgemm_tc_kernel<false, -1, 2>, tzq, tb, p));
+    else MB_CUDA(cudaLaunchKernelEx(&cfg, dgemm_tc_kernel<false, -1, 4>, tzq, tb, p));
+  } else {
+    const long units = (long)p.row_blocks * p.ksplits * cgroups;
+    const int grid = (int)(units < h->sm_count ? units : h->sm_count);
+    void (*kern)(CUtensorMap, CUtensorMap, DtParams) = dgemm_tc_kernel<false, -1, 1>;
+    if (env.trace) kern = dgemm_tc_kernel<true, -1, 1>;
+    else if (env.probe >= 0) kern = dt_probe_kernel(env.probe);
+    kern<<<grid, DT_THREADS, dt_smem_bytes(N), h->stream>>>(tz, tb, p);
+  }
   count_launch();
   MB_LAUNCH_CHECK();
   return 0;

@@ -18,6 +18,7 @@ struct Options {
   int dgemm_mode = 1;      // 0 fp64 SIMT, 1 int8-slice tcgen05
   int dgemm_slices = 0;    // 8-bit digits per column of B in mode 1; 0 = adaptive (6, verified, else 8)
   int crossprod_mode = 2;  // 0 dp4a SIMT, 1 tcgen05 one CTA per tile, 2 tcgen05 CTA pairs (cta_group::2)
+  int wide_cluster = 0;    // B wider than one column group: 1 = clusters with multicast packed tiles (dgemm_tc.cu)
   int pipe_chunks = 4;             // SNP chunks of the host-pointer dgemm_compressed pipeline
   double pipe_min_bytes = 1.0e7;   // ... with at least this many bytes of the snps x n panel per chunk
 };

@@ -98,16 +98,19 @@ def test_dgemm_matches_oracle(gpu_lib, snps, indiv, ncol, mode, slices):
         gpu_lib.mb200_set_dgemm_mode(1, 0)
 
 
+@pytest.mark.parametrize("cluster", [0, 1])
 @pytest.mark.parametrize("slices", [0, 6, 8])
 @pytest.mark.parametrize("snps,indiv,ncol", [(3000, 700, 50), (1200, 2100, 27), (6000, 300, 14)])
-def test_dgemm_wide_b_column_groups(gpu_lib, snps, indiv, ncol, slices):
+def test_dgemm_wide_b_column_groups(gpu_lib, snps, indiv, ncol, slices, cluster):
     """More columns than one MMA's digit rows hold (13 at 6 digits, 10 at 8): the column groups run
     in ONE launch whose units share the packed tiles (examples/gblup/calculate_gblup.jl:89-93 calls
-    with n + p = 50 columns).  Every column against the oracle."""
+    with n + p = 50 columns).  Every column against the oracle; cluster = 1: thread-block clusters with
+    the packed tiles multicast (2 or 4 groups)."""
     from miraculix_b200 import api
     plink, Z, f = simulate.simulate(snps, indiv, seed=snps + ncol, missing=0.01)
     rng = np.random.default_rng(ncol)
     gpu_lib.mb200_set_dgemm_mode(1, slices)
+    gpu_lib.mb200_set_dgemm_wide_cluster(cluster)
     h = api.init_compressed(plink, snps, indiv, f, ncol)
     try:
         for tr, k in (("N", snps), ("T", indiv)):
@@ -119,6 +122,7 @@ def test_dgemm_wide_b_column_groups(gpu_lib, snps, indiv, ncol, slices):
     finally:
         api.free_compressed(h)
         gpu_lib.mb200_set_dgemm_mode(1, 0)
+        gpu_lib.mb200_set_dgemm_wide_cluster(0)
 
 
 def test_dgemm_adaptive_precision(gpu_lib):
