@@ -397,6 +397,17 @@ int mb200_plink2compressed_device(const unsigned char *d_plink, long snps, long 
   clear_status();
   if (!compressed) return fail(-2, __func__, __LINE__, "compressed == NULL");
   *compressed = nullptr;
+  {
+    std::vector<int> devs;
+    MB_CHECK(multi_device_list(&devs));
+    if (devs.size() > 1) {  // sharded: every device copies its SNP rows of the bed from where it lives
+      MultiInput in;
+      in.src = MultiSource::DeviceBed;
+      in.plink = d_plink;
+      in.f = d_f;
+      return multi_create(devs, snps, indiv, max_n, in, compressed);
+    }
+  }
   Handle *h = nullptr;
   MB_CHECK(create_handle(snps, indiv, max_n, &h));
   int rc = repack_from_device(h, d_plink);
@@ -430,8 +441,11 @@ void plink2compressed(char *plink, char *plink_transposed, int snps, int indiv, 
   std::vector<int> devs;
   if (multi_device_list(&devs)) return;
   if (devs.size() > 1) {  // MIRACULIX_NGPUS / CUDA_DEVICE list: SNP blocks sharded over the devices
-    multi_create(devs, snps, indiv, max_n, MultiSource::HostBed, reinterpret_cast<const uint8_t *>(plink), f,
-                 0, compressed);
+    MultiInput in;
+    in.src = MultiSource::HostBed;
+    in.plink = reinterpret_cast<const uint8_t *>(plink);
+    in.f = f;
+    multi_create(devs, snps, indiv, max_n, in, compressed);
     return;
   }
   Handle *h = nullptr;
@@ -456,8 +470,12 @@ int mb200_simulate_compressed(long snps, long indiv, unsigned long long seed, in
   *compressed = nullptr;
   std::vector<int> devs;
   MB_CHECK(multi_device_list(&devs));
-  if (devs.size() > 1)
-    return multi_create(devs, snps, indiv, max_n, MultiSource::Simulated, nullptr, nullptr, seed, compressed);
+  if (devs.size() > 1) {
+    MultiInput in;
+    in.src = MultiSource::Simulated;
+    in.seed = seed;
+    return multi_create(devs, snps, indiv, max_n, in, compressed);
+  }
   Handle *h = nullptr;
   MB_CHECK(create_handle(snps, indiv, max_n, &h, devs.empty() ? -1 : devs[0]));
   uint8_t *d_bed = nullptr;

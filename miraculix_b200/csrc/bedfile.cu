@@ -15,6 +15,7 @@
 #include "../../include/miraculix_b200.h"
 #include "common.cuh"
 #include "handle.h"
+#include "multi.h"
 
 namespace mb200 {
 
@@ -89,7 +90,7 @@ static int bed_inspect(const char *path, long *snps, long *indiv, long *bs) {
 
 // Stream the payload: pinned buffer b is filled by fread while buffer b^1 is in flight to the
 // device; staged chunk -> bed_freq_kernel + repack_chunk on the handle's stream.
-static int bed_stream(Handle *h, const char *path, long bs) {
+static int bed_stream(Handle *h, const char *path, long bs, long row_offset) {
   long rows_per_chunk = (64L << 20) / bs / 512 * 512;  // ~64 MiB, whole 512-SNP tiles
   if (rows_per_chunk < 512) rows_per_chunk = 512;
   if (rows_per_chunk > round_up(h->snps, 512)) rows_per_chunk = round_up(h->snps, 512);
@@ -106,7 +107,7 @@ static int bed_stream(Handle *h, const char *path, long bs) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
   }
   if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "staging buffers: %s", cudaGetErrorString(e));
-  if (!rc && fseek(fp, 3, SEEK_SET) != 0) rc = fail(-22, __func__, __LINE__, "seek failed");
+  if (!rc && fseek(fp, 3 + row_offset * bs, SEEK_SET) != 0) rc = fail(-22, __func__, __LINE__, "seek failed");
   int b = 0;
   for (long s = 0; s < h->snps && !rc; s += rows_per_chunk, b ^= 1) {
     const long cnt = h->snps - s < rows_per_chunk ? h->snps - s : rows_per_chunk;
@@ -135,6 +136,16 @@ static int bed_stream(Handle *h, const char *path, long bs) {
   return rc;
 }
 
+// SNP rows [row_offset, row_offset + h->snps) of the file into the handle: stream + repack +
+// popcount frequencies, then the host copy of f and the row-sum maxima.
+int read_bed_rows(Handle *h, const char *path, long row_offset) {
+  MB_CHECK(bed_stream(h, path, ceil_div(h->indiv, 4), row_offset));
+  h->h_f.resize(h->snps);
+  MB_CUDA(cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * h->snps, cudaMemcpyDeviceToHost, h->stream));
+  MB_CUDA(cudaStreamSynchronize(h->stream));
+  return rowsum_maxima(h);
+}
+
 }  // namespace mb200
 
 using namespace mb200;
@@ -151,26 +162,28 @@ int mb200_bed_shape(const char *bed_path, long *snps, long *indiv) {
 }
 
 int mb200_read_bed(const char *bed_path, int max_n, void **compressed, long *snps, long *indiv) {
+  MB_RANGE();
   clear_status();
   if (!compressed) return fail(-2, __func__, __LINE__, "compressed == NULL");
   *compressed = nullptr;
   long s = 0, n = 0, bs = 0;
   MB_CHECK(bed_inspect(bed_path, &s, &n, &bs));  // before any device work: errors need no GPU
-  Handle *h = nullptr;
-  MB_CHECK(create_handle(s, n, max_n, &h));
-  int rc = bed_stream(h, bed_path, bs);
-  if (!rc) {
-    h->h_f.resize(s);
-    cudaError_t e = cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * s, cudaMemcpyDeviceToHost,
-                                    h->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    if (e != cudaSuccess) rc = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+  std::vector<int> devs;
+  MB_CHECK(multi_device_list(&devs));
+  if (devs.size() > 1) {  // every device streams its own SNP range of the file
+    MultiInput in;
+    in.src = MultiSource::BedFile;
+    in.bed_path = bed_path;
+    MB_CHECK(multi_create(devs, s, n, max_n, in, compressed));
+  } else {
+    Handle *h = nullptr;
+    MB_CHECK(create_handle(s, n, max_n, &h, devs.empty() ? -1 : devs[0]));
+    const int rc = read_bed_rows(h, bed_path, 0);
+    if (rc) { destroy_handle(h); return rc; }
+    *compressed = h;
   }
-  if (!rc) rc = rowsum_maxima(h);
-  if (rc) { destroy_handle(h); return rc; }
   if (snps) *snps = s;
   if (indiv) *indiv = n;
-  *compressed = h;
   return 0;
 }
 

@@ -268,8 +268,12 @@ void multi_destroy(MultiHandle *m) {
   delete m;
 }
 
-int multi_create(const std::vector<int> &devs, long snps, long indiv, int max_n, MultiSource src,
-                 const uint8_t *plink, const double *f, unsigned long long seed, void **out) {
+int multi_create(const std::vector<int> &devs, long snps, long indiv, int max_n, const MultiInput &in,
+                 void **out) {
+  const MultiSource src = in.src;
+  const uint8_t *plink = in.plink;
+  const double *f = in.f;
+  const unsigned long long seed = in.seed;
   *out = nullptr;
   if (snps <= 0 || indiv <= 0) return fail(-2, __func__, __LINE__, "snps=%ld indiv=%ld", snps, indiv);
   if (max_n < 1) max_n = 1;
@@ -321,6 +325,31 @@ int multi_create(const std::vector<int> &devs, long snps, long indiv, int max_n,
     if (src == MultiSource::HostBed) {
       MB_CHECK(repack_from_host(h, plink + m->s_begin[g] * bs));
       MB_CHECK(finish_handle(h, f + m->s_begin[g]));
+    } else if (src == MultiSource::BedFile) {
+      MB_CHECK(read_bed_rows(h, in.bed_path, m->s_begin[g]));
+    } else if (src == MultiSource::DeviceBed) {
+      // the shard's rows of a bed that lives on some device: copied (peer or same device) into a
+      // staging buffer here, repacked, frequencies from the caller (device) or from the counts
+      uint8_t *d_bed = nullptr;
+      MB_CUDA(cudaMalloc(&d_bed, (size_t)m->s_count[g] * bs));
+      cudaError_t e = cudaMemcpyAsync(d_bed, plink + m->s_begin[g] * bs, (size_t)m->s_count[g] * bs,
+                                      cudaMemcpyDefault, h->stream);
+      int r = e == cudaSuccess ? 0 : fail((int)e, __func__, __LINE__, "bed shard copy: %s", cudaGetErrorString(e));
+      if (!r) r = repack_from_device(h, d_bed);
+      if (!r && f) {
+        h->h_f.resize(m->s_count[g]);
+        e = cudaMemcpyAsync(h->d_f, f + m->s_begin[g], sizeof(double) * m->s_count[g], cudaMemcpyDefault, h->stream);
+        if (e == cudaSuccess)
+          e = cudaMemcpyAsync(h->h_f.data(), h->d_f, sizeof(double) * m->s_count[g], cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) r = fail((int)e, __func__, __LINE__, "%s", cudaGetErrorString(e));
+        if (!r) r = rowsum_maxima(h);
+      } else if (!r) {
+        r = finish_handle(h, nullptr);
+      }
+      cudaStreamSynchronize(h->stream);
+      cudaFree(d_bed);
+      MB_CHECK(r);
     } else {
       uint8_t *d_bed = nullptr;
       MB_CUDA(cudaMalloc(&d_bed, (size_t)m->s_count[g] * bs));

@@ -30,9 +30,17 @@ int multi_set_devices(int n, const int *devs);
 
 MultiHandle *as_multi(void *p);  // nullptr (no status) unless p is a live multi-device handle
 
-enum class MultiSource { HostBed, Simulated };
-int multi_create(const std::vector<int> &devs, long snps, long indiv, int max_n, MultiSource src,
-                 const uint8_t *plink, const double *f, unsigned long long seed, void **out);
+enum class MultiSource { HostBed, Simulated, BedFile, DeviceBed };
+struct MultiInput {
+  MultiSource src = MultiSource::HostBed;
+  const uint8_t *plink = nullptr;    // HostBed: host bed payload;  DeviceBed: device pointer (any device)
+  const double *f = nullptr;         // HostBed: host frequencies;  DeviceBed: device pointer or nullptr
+  unsigned long long seed = 0;       // Simulated
+  const char *bed_path = nullptr;    // BedFile
+};
+int multi_create(const std::vector<int> &devs, long snps, long indiv, int max_n, const MultiInput &in,
+                 void **out);
+int read_bed_rows(Handle *h, const char *path, long row_offset);  // bedfile.cu
 void multi_destroy(MultiHandle *m);
 int multi_dgemm_host(MultiHandle *m, int trans, int n, const double *B, long ldb, double *C, long ldc);
 int multi_cg_solve(MultiHandle *m, const double *b, double *x, double lambda, double tol,

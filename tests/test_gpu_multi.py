@@ -425,3 +425,41 @@ def test_concurrent_handles_on_one_device(gpu_lib):
     finally:
         for h in hs:
             api.free_compressed(h)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_read_bed_and_device_bed_sharded(gpu_lib, tmp_path, world):
+    """mb200_read_bed and mb200_plink2compressed_device with a device list: every device streams /
+    copies its own SNP range; shards bit-exact, frequencies = read_bed's popcount rule (file) or the
+    counts (device bed, no f given), products against the oracle."""
+    import torch
+    from oracle import bedfile
+    from miraculix_b200 import api
+    snps, indiv, ncol = 2600, 517, 3
+    plink, Z, f = simulate.simulate(snps, indiv, seed=12, missing=0.02)
+    path = bedfile.write_bed(str(tmp_path / "geno"), plink, snps, indiv)
+    p_o, f_o, s_o, n_o = bedfile.read_bed(path)
+    api.set_devices(device_list(world))
+    h, fq, s, n = api.read_bed_compressed(path, ncol)
+    d_plink = torch.from_numpy(plink).cuda()
+    h2 = C.c_void_p(None)
+    api._check(gpu_lib.mb200_plink2compressed_device(d_plink.data_ptr(), snps, indiv, None, ncol, C.byref(h2)),
+               "plink2compressed_device")
+    try:
+        assert (s, n) == (snps, indiv) and np.array_equal(fq, f_o)
+        for hh in (h, h2):
+            assert gpu_lib.mb200_shard_count(hh) == world
+            for sub, b, c in api.shards(hh):
+                sm, im, cnt = api.download_layout(sub)
+                sm_o, im_o = cport.repack(plink[b:b + c], c, indiv)
+                assert np.array_equal(sm, sm_o) and np.array_equal(im, im_o)
+        f2 = api.get_compressed_freq(h2, snps)
+        assert np.array_equal(f2, cport.allele_counts(plink, snps, indiv) / (2.0 * indiv))
+        B = np.asfortranarray(np.random.default_rng(1).standard_normal((snps, ncol)))
+        assert relerr(api.dgemm_compressed("N", h, B, snps, indiv),
+                      cport.dgemm_compressed("N", plink, snps, indiv, f_o, B, True)) <= TOL
+        assert relerr(api.dgemm_compressed("N", h2, B, snps, indiv),
+                      cport.dgemm_compressed("N", plink, snps, indiv, f2, B, True)) <= TOL
+    finally:
+        api.free_compressed(h)
+        api.free_compressed(h2)
