@@ -111,3 +111,29 @@ def test_product_never_touches_the_oracle(lib):
     mods = _run("import sys, miraculix_b200, miraculix_b200.api, miraculix_b200.sharded;"
                 "print([m for m in sys.modules if m.split('.')[0] == 'oracle'])")
     assert mods.returncode == 0 and mods.stdout.strip() == "[]", mods.stdout + mods.stderr
+
+
+def test_device_list_without_a_gpu_fails_loudly(lib):
+    """MIRACULIX_NGPUS / CUDA_DEVICE lists / mb200_set_devices select the sharded path; without a CUDA
+    device every entry point refuses with a message and a NULL handle (no CPU path, no crash).  Runs
+    in a subprocess with the GPUs hidden, so it means the same thing on a GPU box."""
+    code = (
+        "import os, numpy as np, ctypes as C\n"
+        "os.environ['CUDA_VISIBLE_DEVICES'] = ''\n"
+        "from miraculix_b200 import api\n"
+        "L = api.load_library()\n"
+        "plink = np.zeros((600, 3), dtype=np.uint8); f = np.zeros(600); h = C.c_void_p(None)\n"
+        "for how in ('env', 'list', 'api'):\n"
+        "    os.environ.pop('MIRACULIX_NGPUS', None); os.environ.pop('CUDA_DEVICE', None); api.set_devices(None)\n"
+        "    if how == 'env': os.environ['MIRACULIX_NGPUS'] = '2'\n"
+        "    if how == 'list': os.environ['CUDA_DEVICE'] = '0,1'\n"
+        "    if how == 'api': api.set_devices([0, 1])\n"
+        "    L.plink2compressed(plink.ctypes.data, plink.ctypes.data, 600, 12, f.ctypes.data, 1, C.byref(h))\n"
+        "    assert not h.value and L.mb200_last_status() != 0, how\n"
+        "    ans = np.zeros((12, 12))\n"
+        "    assert L.snp_multiply_gpu(plink.ctypes.data, 12, 12, ans.ctypes.data, False) == 1\n"
+        "assert L.mb200_shard_count(None) == -1\n"
+        "print('refused')\n")
+    r = _run(code)
+    assert r.returncode == 0 and "refused" in r.stdout, r.stdout + r.stderr
+    assert "no usable CUDA device" in r.stderr
