@@ -218,6 +218,8 @@ void destroy_handle(Handle *h) {
   for (int i = 0; i < Handle::kPipeMax; i++)
     if (h->ev_pipe[i]) cudaEventDestroy(h->ev_pipe[i]);
   h->stager.destroy();
+  for (int i = 0; i < 2; i++)
+    if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]);
   for (int i = 0; i < Handle::kEvRing; i++) {
     if (h->ev_begin[i]) cudaEventDestroy(h->ev_begin[i]);
     if (h->ev_end[i]) cudaEventDestroy(h->ev_end[i]);
@@ -263,6 +265,7 @@ int create_handle(long snps, long indiv, int max_n, Handle **out, int device) {
   for (int i = 0; i < Handle::kPipeMax; i++)
     H_CUDA(cudaEventCreateWithFlags(&h->ev_pipe[i], cudaEventDisableTiming));
   H_CUDA(cudaMallocHost(&h->h_pipe, 64));
+  for (int i = 0; i < 2; i++) H_CUDA(cudaEventCreate(&h->ev_copy[i]));
   for (int i = 0; i < Handle::kEvRing; i++) {
     H_CUDA(cudaEventCreate(&h->ev_begin[i]));
     H_CUDA(cudaEventCreate(&h->ev_end[i]));

@@ -951,13 +951,38 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
   h->last_slices = S;
   h->last_adaptive = adaptive;
 
+  // the previous call's copy measurement (its streams were drained before it returned)
+  if (h->copy_dir >= 0) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, h->ev_copy[0], h->ev_copy[1]) == cudaSuccess && ms > 0) {
+      const double gbs = h->copy_bytes / (ms * 1e6);
+      h->link_gbs[h->copy_dir] = h->link_gbs[h->copy_dir] > 0 ? 0.5 * (h->link_gbs[h->copy_dir] + gbs) : gbs;
+    } else {
+      cudaGetLastError();
+    }
+    h->copy_dir = -1;
+  }
   // chunks of the SNP axis: only worth it when the big panel takes a while on PCIe
   int chunks = options().pipe_chunks;
   if (chunks > Handle::kPipeMax) chunks = Handle::kPipeMax;
-  // at least pipe_min_bytes of panel per chunk: a chunk costs ~50 us of small kernels and tails,
-  // which a PCIe copy shorter than ~0.2 ms cannot win back (measured at the 8-GPU shard size)
-  if (options().pipe_min_bytes > 0) {
-    const double per = (double)h->snps * n * 8.0 / options().pipe_min_bytes;
+  const int dir = trans ? 1 : 0;
+  const bool direct = trans ? c_pin : b_pin;  // page-locked caller panel: plain async DMA
+  const double panel_bytes = (double)h->snps * n * 8.0;
+  if (options().pipe_min_bytes > 0 && direct && h->link_gbs[dir] > 0 && (pipe_in || pipe_out)) {
+    // measured link rate known: c chunks of weights 1 : 2 : ... : c expose copy / (c (c + 1) / 2) of
+    // the copy and cost ~50 us each of small kernels and tails (scripts/dbg/chunk_sweep.py)
+    const double copy_ms = panel_bytes / (h->link_gbs[dir] * 1e6);
+    int best = 1;
+    double best_cost = copy_ms;
+    for (int c = 2; c <= chunks; c++) {
+      const double cost = copy_ms / (0.5 * c * (c + 1)) + 0.05 * (c - 1);
+      if (cost < best_cost) { best_cost = cost; best = c; }
+    }
+    chunks = best;
+  } else if (options().pipe_min_bytes > 0) {
+    // at least pipe_min_bytes of panel per chunk: a chunk costs ~50 us of small kernels and tails,
+    // which a PCIe copy shorter than ~0.2 ms cannot win back (measured at the 8-GPU shard size)
+    const double per = panel_bytes / options().pipe_min_bytes;
     if (per < chunks) chunks = (int)per;
   }
   if (chunks < 1) chunks = 1;
@@ -991,7 +1016,14 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
     for (int i = 0; i < chunks; i++) {
       const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
       if (pipe_in) {  // staged uploads block the host while the kernels of chunk i-1 run
+        const bool measure = b_pin && i == chunks - 1;  // the largest chunk
+        if (measure) MB_CUDA(cudaEventRecord(h->ev_copy[0], h->copy_stream));
         MB_CHECK(panel_h2d(sg, b_pin, h->d_B + s0, k, B + s0, ldb, cnt, n, h->copy_stream));
+        if (measure) {
+          MB_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+          h->copy_dir = 0;
+          h->copy_bytes = (double)cnt * n * 8.0;
+        }
         MB_CUDA(cudaEventRecord(h->ev_pipe[i], h->copy_stream));
         MB_CUDA(cudaStreamWaitEvent(h->stream, h->ev_pipe[i], 0));
         mark("upload enqueued", i);
@@ -1014,7 +1046,15 @@ int dgemm_tc_host_pipelined(Handle *h, int trans, int n, const double *B, long l
     auto download = [&](int i) -> int {
       const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];
       MB_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_pipe[i], 0));
-      return panel_d2h(sg, c_pin, C + s0, ldc, dC + s0, ldC, cnt, n, h->copy_stream);
+      const bool measure = c_pin && i == 0;  // the largest chunk; the clock starts when its kernels are done
+      if (measure) MB_CUDA(cudaEventRecord(h->ev_copy[0], h->copy_stream));
+      MB_CHECK(panel_d2h(sg, c_pin, C + s0, ldc, dC + s0, ldC, cnt, n, h->copy_stream));
+      if (measure) {
+        MB_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+        h->copy_dir = 1;
+        h->copy_bytes = (double)cnt * n * 8.0;
+      }
+      return 0;
     };
     for (int i = 0; i < chunks; i++) {
       const long s0 = bnd[i], cnt = bnd[i + 1] - bnd[i];

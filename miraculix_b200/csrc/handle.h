@@ -64,6 +64,13 @@ struct Handle {
   static constexpr int kPipeMax = 16;
   cudaEvent_t ev_pipe[kPipeMax] = {nullptr};
   void *h_pipe = nullptr;  // pinned word: the precision flag travels back with the result
+  // measured rate of this handle's pinned host copies (GB/s; [0] H2D of 'N', [1] D2H of 'T'): events
+  // around the largest chunk of the last call; the chunk count of the next call follows from it
+  // (boxes whose GPUs share host links deliver a fraction of a link per device)
+  cudaEvent_t ev_copy[2] = {nullptr, nullptr};
+  double link_gbs[2] = {0, 0};
+  int copy_dir = -1;       // direction of the measurement in flight, -1 = none
+  double copy_bytes = 0;
   // ring of event pairs around the MAIN kernel of each dgemm_compressed call (bench.py reads
   // the per-launch durations of the timed region through mb200_dgemm_kernel_times)
   static constexpr int kEvRing = 128;

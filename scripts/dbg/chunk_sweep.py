@@ -27,4 +27,9 @@ for chunks in (1, 2, 3, 4, 6):
     n = best(lambda: lib.dgemm_compressed(b"N", h, ncol, Bn.data_ptr(), snps, Cn.data_ptr(), indiv))
     t = best(lambda: lib.dgemm_compressed(b"T", h, ncol, Bt.data_ptr(), indiv, Ct.data_ptr(), snps))
     print("chunks %d: N best %.3f median %.3f | T best %.3f median %.3f | step %.3f" % (chunks, n[0], n[1], t[0], t[1], n[0] + t[0]), flush=True)
+lib.mb200_set_pipeline(4, 1.0e7)   # default policy: chunk count from the measured link rate
+for rep in range(2):
+    n = best(lambda: lib.dgemm_compressed(b"N", h, ncol, Bn.data_ptr(), snps, Cn.data_ptr(), indiv))
+    t = best(lambda: lib.dgemm_compressed(b"T", h, ncol, Bt.data_ptr(), indiv, Ct.data_ptr(), snps))
+    print("default policy: N best %.3f median %.3f | T best %.3f median %.3f | step %.3f" % (n[0], n[1], t[0], t[1], n[0] + t[0]), flush=True)
 lib.free_compressed(C.byref(h))
