@@ -168,6 +168,21 @@ int mb200_set_crossprod_mode(int mode);
  * handle's stream (mb200_stream).  trans: 0 = 'N', 1 = 'T'.  Returns 0 / error code. */
 int mb200_dgemm_compressed_device(int trans, void *compressed, int n, const double *dB, long ldb,
                                   double *dC, long ldc);
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The fp64 dgemm_compressed on DEVICE pointers dB, dC, asynchronous on the handle's
+ * stream like mb200_dgemm_compressed_device, but this call allocates nothing: the centring
+ * scalars, which the ordinary path keeps in scratch owned by the handle, live in a static
+ * __device__ array of MB200_NOALLOC_MAX_COLS = 1024 doubles (8 KiB on every GPU that loads the
+ * library, until exit).  n > 1024 is refused with status -2 and C untouched (n is not bound by
+ * the handle's max_n).  The array is shared by ALL calls and cleared at the start of each one:
+ * calls that overlap on one GPU (other streams, other handles) race on it -- order them.
+ * Single-device handles only; honours setOptions_compressed's centring switch, always computes
+ * with the fp64 kernel (mb200_set_dgemm_mode does not apply). */
+#define MB200_NOALLOC_MAX_COLS 1024
+int mb200_dgemm_compressed_noalloc(int trans, void *compressed, int n, const double *dB, long ldb,
+                                   double *dC, long ldc);
+int mb200_noalloc_max_cols(void); /* = MB200_NOALLOC_MAX_COLS of the loaded library */
 /* Same product with each panel on the host OR on the device (flags): host panels are copied over
  * PCIe, pipelined against the kernels like dgemm_compressed.  Blocking (returns after the
  * handle's stream has drained) unless both panels are on the device.  Used by SNP-sharded callers:

@@ -45,6 +45,9 @@ SIGNATURES = {
     "mb200_set_pipeline": (C.c_int, [C.c_int, C.c_double]),
     "mb200_dgemm_compressed_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
                                                 C.c_void_p, C.c_long]),
+    "mb200_dgemm_compressed_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
+                                                 C.c_void_p, C.c_long]),
+    "mb200_noalloc_max_cols": (C.c_int, []),
     "mb200_dgemm_compressed_mixed": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
                                                C.c_int, C.c_void_p, C.c_long, C.c_int]),
     "mb200_stream": (C.c_void_p, [C.c_void_p]),

@@ -203,8 +203,8 @@ static int launch_fp64(Handle *h, const uint8_t *A, long pitch, long rows, long 
   return 0;
 }
 
-static int dgemm_fp64_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
-                             long ldc) {
+int dgemm_fp64_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC,
+                      long ldc) {
   const uint8_t *A = trans ? h->d_snp_major : h->d_indiv_major;
   const long pitch = trans ? h->pitch_s : h->pitch_i;
   const long rows = trans ? h->snps : h->indiv, K = trans ? h->indiv : h->snps;
