@@ -19,6 +19,7 @@
 #define MIRACULIX_B200_H
 
 #include <stdbool.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -205,6 +206,11 @@ int mb200_sync(void *compressed);
 /* Developer aid: with MB200_TRACE=1 the tensor-core dgemm kernel accumulates clock64() segments
  * of one expander warp ([0..7]) and of the MMA warp ([16..19]) of CTA 0; this reads them. */
 int mb200_debug_read_trace(long long *out, int n);
+/* Developer aid: the host copy pool that stages pageable caller memory (csrc/stager.h), callable
+ * without a GPU: dst[r + c*dpitch] = src[r + c*spitch] for r < width bytes, c < height.  Any
+ * number of threads may call it at the same time (they share the MB200_COPY_THREADS helpers). */
+int mb200_debug_parallel_copy(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                              size_t height);
 
 /* Build a handle from a bed payload that already lives on the device (same layout as the
  * host one).  d_f may be NULL: then f is computed on the device from the allele counts. */

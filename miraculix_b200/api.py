@@ -51,6 +51,8 @@ SIGNATURES = {
     "mb200_dgemm_compressed_mixed": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,
                                                C.c_int, C.c_void_p, C.c_long, C.c_int]),
     "mb200_stream": (C.c_void_p, [C.c_void_p]),
+    "mb200_debug_parallel_copy": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t,
+                                            C.c_size_t]),
     "mb200_sync": (C.c_int, [C.c_void_p]),
     "mb200_dgemm_last_precision": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "mb200_debug_read_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),

@@ -12,9 +12,11 @@
 namespace mb200 {
 
 // ---------------------------------------------------------------------------------------------
-// Copy pool: helper threads that take slices of one 2-D copy.  Several device worker threads
-// (multi.cu) may call parallel_copy_2d at the same time; calls are serialised on the pool (the
-// helpers are a shared resource: memory bandwidth, not core count, is what they multiply).
+// Copy pool: helper threads that take pieces of 2-D copies.  Several device worker threads
+// (multi.cu, crossprod_host.cu) stage at the same time: every call registers its copy as a job,
+// works on it itself, and idle helpers join whichever registered job still has pieces left, so
+// eight concurrent callers and fifteen helpers keep about twenty cores copying (a result of
+// 80 GB leaving eight devices is bound by the host memcpy otherwise, not by the links).
 // ---------------------------------------------------------------------------------------------
 namespace {
 
@@ -23,7 +25,8 @@ struct CopyJob {
   const uint8_t *src = nullptr;
   size_t dpitch = 0, spitch = 0, width = 0, height = 0;
   size_t pieces = 0, piece_bytes = 0;  // the flattened width*height bytes are cut into pieces
-  std::atomic<size_t> next{0}, done{0};
+  std::atomic<size_t> next{0};
+  int helpers_in = 0;                  // helpers working on this job (guarded by the pool mutex)
 };
 
 void copy_piece(const CopyJob &j, size_t piece) {
@@ -45,23 +48,22 @@ class CopyPool {
     return pool;
   }
   int helpers() const { return (int)threads_.size(); }
-  // false: the helpers are busy with another caller's copy (several device workers stage at the
-  // same time) -- the caller then copies inline, which is the parallelism wanted in that case
-  bool run(CopyJob &job) {
-    std::unique_lock<std::mutex> call(call_mu_, std::try_to_lock);
-    if (!call.owns_lock()) return false;
+  // Returns when every piece of the job is copied.  Any number of callers at a time.
+  void run(CopyJob &job) {
     {
       std::lock_guard<std::mutex> lk(mu_);
-      job_ = &job;
-      gen_++;
+      jobs_.push_back(&job);
     }
     cv_.notify_all();
-    work(job);
-    // wait until every piece is done AND every helper has left the job
+    work(job);  // the caller's share; returns once every piece has been TAKEN
     std::unique_lock<std::mutex> lk(mu_);
-    done_cv_.wait(lk, [&] { return job.done.load() == job.pieces && active_ == 0; });
-    job_ = nullptr;
-    return true;
+    for (size_t i = 0; i < jobs_.size(); i++)
+      if (jobs_[i] == &job) {  // no helper can join from here on
+        jobs_[i] = jobs_.back();
+        jobs_.pop_back();
+        break;
+      }
+    done_cv_.wait(lk, [&] { return job.helpers_in == 0; });  // the helpers inside have finished theirs
   }
 
  private:
@@ -71,10 +73,11 @@ class CopyPool {
     else {
       const unsigned hw = std::thread::hardware_concurrency();
       n = (int)(hw / 2);
-      if (n > 8) n = 8;
-      n -= 1;  // the caller copies too
+      if (n > 16) n = 16;
+      n -= 1;  // the callers copy too
     }
     if (n < 0) n = 0;
+    if (n > 64) n = 64;
     for (int i = 0; i < n; i++) threads_.emplace_back([this] { loop(); });
   }
   ~CopyPool() {
@@ -87,39 +90,42 @@ class CopyPool {
   }
   static void work(CopyJob &job) {
     for (;;) {
-      const size_t p = job.next.fetch_add(1);
+      const size_t p = job.next.fetch_add(1, std::memory_order_relaxed);
       if (p >= job.pieces) break;
       copy_piece(job, p);
-      job.done.fetch_add(1);
     }
   }
+  // a registered job that still has untaken pieces; starts at a rotating position so that the
+  // helpers spread over concurrent jobs (mu_ held)
+  CopyJob *pick() {
+    const size_t n = jobs_.size();
+    for (size_t i = 0; i < n; i++) {
+      CopyJob *j = jobs_[(rr_ + i) % n];
+      if (j->next.load(std::memory_order_relaxed) < j->pieces) {
+        rr_ = (rr_ + i + 1) % n;
+        return j;
+      }
+    }
+    return nullptr;
+  }
   void loop() {
-    unsigned long long seen = 0;
+    std::unique_lock<std::mutex> lk(mu_);
     for (;;) {
       CopyJob *job = nullptr;
-      {
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_.wait(lk, [&] { return quit_ || gen_ != seen; });
-        if (quit_) return;
-        seen = gen_;
-        job = job_;
-        if (job) active_++;
-      }
-      if (!job) continue;
+      cv_.wait(lk, [&] { return quit_ || (job = pick()) != nullptr; });
+      if (quit_) return;
+      job->helpers_in++;
+      lk.unlock();
       work(*job);
-      {
-        std::lock_guard<std::mutex> lk(mu_);
-        active_--;
-      }
-      done_cv_.notify_all();
+      lk.lock();
+      if (--job->helpers_in == 0) done_cv_.notify_all();
     }
   }
   std::vector<std::thread> threads_;
-  std::mutex mu_, call_mu_;
+  std::mutex mu_;
   std::condition_variable cv_, done_cv_;
-  CopyJob *job_ = nullptr;
-  unsigned long long gen_ = 0;
-  int active_ = 0;
+  std::vector<CopyJob *> jobs_;
+  size_t rr_ = 0;
   bool quit_ = false;
 };
 
@@ -149,11 +155,7 @@ void parallel_copy_2d(void *dst, size_t dpitch, const void *src, size_t spitch, 
   if (pieces > 4 * parts) pieces = 4 * parts;
   job.piece_bytes = ((total + pieces - 1) / pieces + 63) & ~(size_t)63;
   job.pieces = (total + job.piece_bytes - 1) / job.piece_bytes;
-  if (!pool.run(job)) {
-    job.pieces = 1;
-    job.piece_bytes = total;
-    copy_piece(job, 0);
-  }
+  pool.run(job);
 }
 
 bool host_is_pinned(const void *p) {
@@ -298,3 +300,11 @@ int panel_d2h(Stager *sg, bool pinned, double *h, long ld_h, const double *d, lo
 }
 
 }  // namespace mb200
+
+// Developer aid for the CPU tests of the copy pool (no GPU involved).
+extern "C" int mb200_debug_parallel_copy(void *dst, size_t dpitch, const void *src, size_t spitch,
+                                         size_t width, size_t height) {
+  if (!dst || !src || dpitch < width || spitch < width) return -2;
+  mb200::parallel_copy_2d(dst, dpitch, src, spitch, width, height);
+  return 0;
+}

@@ -14,7 +14,8 @@
 namespace mb200 {
 
 // dst[r + c*dpitch] = src[r + c*spitch], width bytes per column, split over the copy pool
-// (MB200_COPY_THREADS helper threads, default min(8, cores/2); the caller takes part).
+// (MB200_COPY_THREADS helper threads, default min(16, cores/2) - 1; the callers take part, and
+// concurrent calls share the helpers).
 void parallel_copy_2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
                       size_t height);
 

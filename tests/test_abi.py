@@ -137,3 +137,38 @@ def test_device_list_without_a_gpu_fails_loudly(lib):
     r = _run(code)
     assert r.returncode == 0 and "refused" in r.stdout, r.stdout + r.stderr
     assert "no usable CUDA device" in r.stderr
+
+
+def test_copy_pool_serves_concurrent_callers(lib):
+    """The staging copy pool (csrc/stager.cu): eight threads copy 2-D blocks of different shapes at
+    the same time, many times over, sharing the helper threads -- every destination must equal its
+    source, bytes outside the copied columns must stay untouched (host logic, no GPU)."""
+    import threading
+
+    import numpy as np
+    errors = []
+
+    def worker(seed):
+        rng = np.random.default_rng(seed)
+        for it in range(12):
+            width = int(rng.integers(1, 3_000_000)) if it % 3 else int(rng.integers(1, 5000))
+            height = int(rng.integers(1, 9)) if width > 100_000 else int(rng.integers(1, 700))
+            spitch, dpitch = width + int(rng.integers(0, 64)), width + int(rng.integers(0, 64))
+            src = rng.integers(0, 256, size=spitch * height, dtype=np.uint8)
+            dst = np.full(dpitch * height, 0xA5, dtype=np.uint8)
+            rc = lib.mb200_debug_parallel_copy(dst.ctypes.data, dpitch, src.ctypes.data, spitch, width, height)
+            s2, d2 = src.reshape(height, spitch), dst.reshape(height, dpitch)
+            if rc != 0 or not np.array_equal(d2[:, :width], s2[:, :width]) or not np.all(d2[:, width:] == 0xA5):
+                errors.append((seed, it, width, height, rc))
+
+    threads = [threading.Thread(target=worker, args=(s,)) for s in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors[:3]
+    big = np.arange(64 << 20, dtype=np.uint8)          # one large flat copy: cut into many pieces
+    out = np.zeros_like(big)
+    assert lib.mb200_debug_parallel_copy(out.ctypes.data, big.size, big.ctypes.data, big.size, big.size, 1) == 0
+    assert np.array_equal(out, big)
+    assert lib.mb200_debug_parallel_copy(None, 8, big.ctypes.data, 8, 8, 1) != 0
