@@ -612,24 +612,37 @@ def run_wide(args, lib, api, dev):
 def run_small(lib, api):
     """BASELINE configs[0]: dgemm_compressed 'n', ncol = 1, 10k SNPs x 1k individuals -- the
     reference's own test case (tests/dgemm_compressed); latency of the C-ABI call with pageable
-    host vectors.  Reported, not a roofline case (the matrix is 2.5 MB)."""
+    host vectors.  Reported, not a roofline case (the matrix is 2.5 MB).  The default configuration
+    routes a call this small to the one-kernel path (csrc/dgemm_small.cu); the same call through
+    the tcgen05 digit-slice path (small limit 0) is timed beside it and the two results compared."""
     import numpy as np
     snps, indiv = 10_000, 1_000
     h = api.simulate_compressed(snps, indiv, 5, 1)
     rng = np.random.default_rng(1)
     B = rng.standard_normal(snps)
-    Cout = np.empty(indiv)
-    ts = []
-    for it in range(120):
-        t0 = time.perf_counter()
-        lib.dgemm_compressed(b"N", h, 1, B.ctypes.data, snps, Cout.ctypes.data, indiv)
-        if it >= 20:
-            ts.append(time.perf_counter() - t0)
-    ok = lib.mb200_last_status() == 0
+    res, outs, ok = {}, {}, True
+    for name, limit in (("default", 4.0e7), ("tensor_core", 0.0)):
+        lib.mb200_set_dgemm_small_limit(limit)
+        Cout = np.empty(indiv)
+        ts = []
+        for it in range(120):
+            t0 = time.perf_counter()
+            lib.dgemm_compressed(b"N", h, 1, B.ctypes.data, snps, Cout.ctypes.data, indiv)
+            if it >= 20:
+                ts.append(time.perf_counter() - t0)
+        ok = ok and lib.mb200_last_status() == 0
+        res[name], outs[name] = ts, Cout
+    lib.mb200_set_dgemm_small_limit(4.0e7)
     lib.free_compressed(C.byref(h))
+    ts = res["default"]
+    diff = float(np.abs(outs["default"] - outs["tensor_core"]).max() / np.abs(outs["tensor_core"]).max())
     return {"workload": "dgemm_compressed 'n', ncol=1, 10000 SNPs x 1000 individuals (BASELINE configs[0])",
             "ms_median": statistics.median(ts) * 1e3, "ms_best": min(ts) * 1e3, "calls": len(ts),
-            "value": snps * indiv / statistics.median(ts), "unit": UNIT, "ok": ok,
+            "value": snps * indiv / statistics.median(ts), "unit": UNIT, "ok": ok and diff <= 1e-10,
+            "path": "one fused fp64 kernel (csrc/dgemm_small.cu), the default below 4e7 genotype-column products",
+            "tensor_core_path": {"ms_median": statistics.median(res["tensor_core"]) * 1e3,
+                                 "ms_best": min(res["tensor_core"]) * 1e3,
+                                 "max_rel_diff_of_results": diff},
             "api": "dgemm_compressed() C-ABI, pageable host vectors, wall clock per call"}
 
 

@@ -160,6 +160,13 @@ int mb200_set_dgemm_wide_cluster(int on);
  * panel (default 1e7: a 10 MB panel is not cut at all; 0 = always `chunks`; negative = keep).
  * Results do not depend on the chunking beyond fp64 summation order. */
 int mb200_set_pipeline(int chunks, double min_bytes);
+/* Host-pointer dgemm_compressed on SMALL problems (snps * indiv * n <= products, panels below
+ * 4 MB; default 4e7, env MB200_SMALL_LIMIT; 0 = never) with the default precision policy
+ * (mb200_set_dgemm_mode(1, 0)): one fused fp64 kernel -- centring and product -- between one
+ * upload and one download, because such calls are bound by the number of API calls, not by the
+ * GPU (BASELINE configs[0], the reference's tests/dgemm_compressed case).  fp64 FMAs in a fixed
+ * order: reproducible bit for bit; mb200_dgemm_last_precision then reports 0 digits. */
+int mb200_set_dgemm_small_limit(double products);
 /* 0: SIMT dp4a crossproduct, 1: tcgen05 int8 crossproduct, one CTA per 128 x 256 tile,
  * 2 (default): tcgen05 cta_group::2, CTA pairs on 256 x 256 tiles (full-matrix products and the
  * partitioned GRM, whose pairs take two consecutive row tiles of the partition). */

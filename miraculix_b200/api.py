@@ -41,6 +41,7 @@ SIGNATURES = {
     "mb200_kernel_launches": (C.c_ulonglong, []),
     "mb200_set_dgemm_mode": (C.c_int, [C.c_int, C.c_int]),
     "mb200_set_crossprod_mode": (C.c_int, [C.c_int]),
+    "mb200_set_dgemm_small_limit": (C.c_int, [C.c_double]),
     "mb200_set_dgemm_wide_cluster": (C.c_int, [C.c_int]),
     "mb200_set_pipeline": (C.c_int, [C.c_int, C.c_double]),
     "mb200_dgemm_compressed_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_long,

@@ -13,7 +13,7 @@ OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmiraculix_b200.so")
 SOURCES = ["abi.cu", "repack.cu", "dgemm.cu", "dgemm_tc.cu", "crossprod.cu", "crossprod_tc.cu",
            "crossprod_host.cu", "multi.cu", "stager.cu", "solver.cu", "bedfile.cu", "dense_solve.cu",
-           "sparse_plink.cu", "noalloc.cu"]
+           "sparse_plink.cu", "noalloc.cu", "dgemm_small.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-pthread", "-Xptxas", "-v", "--expt-relaxed-constexpr"]

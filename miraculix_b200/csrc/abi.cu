@@ -120,6 +120,7 @@ Options &options() {
     if (const char *e = getenv("MB200_DGEMM_SLICES")) v.dgemm_slices = atoi(e);
     if (const char *e = getenv("MB200_CROSSPROD_MODE")) v.crossprod_mode = atoi(e);
     if (const char *e = getenv("MB200_WIDE_CLUSTER")) v.wide_cluster = atoi(e) != 0;
+    if (const char *e = getenv("MB200_SMALL_LIMIT")) v.small_limit = atof(e);
     if (const char *e = getenv("MB200_PIPE_CHUNKS")) v.pipe_chunks = atoi(e);
     if (const char *e = getenv("MB200_PIPE_MIN_BYTES")) v.pipe_min_bytes = atof(e);
     return v;
@@ -360,6 +361,10 @@ int mb200_set_pipeline(int chunks, double min_bytes) {
   if (min_bytes >= 0) o.pipe_min_bytes = min_bytes;
   return 0;
 }
+int mb200_set_dgemm_small_limit(double products) {
+  if (products >= 0) options().small_limit = products;
+  return 0;
+}
 int mb200_set_crossprod_mode(int mode) {
   if (mode >= 0 && mode <= 2) options().crossprod_mode = mode;
   return 0;
@@ -591,6 +596,8 @@ static int dgemm_host(Handle *h, int trans, int n, const double *B, long ldb, do
     return fail(-2, __func__, __LINE__, "leading dimension too small: ldb=%ld (need %ld) ldc=%ld (need %ld)",
                 ldb, k, ldc, m);
   if (n <= 0) return 0;
+  if (dgemm_small_applies(h, n))  // latency bound: one fused kernel, one synchronisation
+    return dgemm_small_host(h, trans, n, B, ldb, C, ldc);
   if (options().dgemm_mode == 1)  // tensor-core path: PCIe copies pipelined against the kernels
     return dgemm_tc_host_pipelined(h, trans, n, B, ldb, C, ldc, 0, 0);
   const bool b_pin = host_is_pinned(B), c_pin = host_is_pinned(C);

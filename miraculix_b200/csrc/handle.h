@@ -19,6 +19,7 @@ struct Options {
   int dgemm_slices = 0;    // 8-bit digits per column of B in mode 1; 0 = adaptive (6, verified, else 8)
   int crossprod_mode = 2;  // 0 dp4a SIMT, 1 tcgen05 one CTA per tile, 2 tcgen05 CTA pairs (cta_group::2)
   int wide_cluster = 0;    // B wider than one column group: 1 = clusters with multicast packed tiles (dgemm_tc.cu)
+  double small_limit = 4.0e7;      // host-pointer dgemm_compressed with snps*indiv*n at most this: one fused fp64 kernel (dgemm_small.cu)
   int pipe_chunks = 4;             // SNP chunks of the host-pointer dgemm_compressed pipeline
   double pipe_min_bytes = 1.0e7;   // ... with at least this many bytes of the snps x n panel per chunk
 };
@@ -108,6 +109,11 @@ int simulate_plink(uint8_t *d_plink, long snps, long indiv, unsigned long long s
                    cudaStream_t stream, long s_offset = 0);
 int freq_from_counts(Handle *h);  // d_f = counts / (2 indiv)
 int rowsum_maxima(Handle *h);     // fills h->rowsum_max (synchronises the stream)
+
+// dgemm_small.cu: latency path of the host-pointer call on small problems
+bool dgemm_small_applies(const Handle *h, int n);
+int dgemm_small_host(Handle *h, int trans, int n, const double *B, long ldb, double *C, long ldc);
+int dgemm_small_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);
 
 // dgemm.cu
 int dgemm_device(Handle *h, int trans, int n, const double *dB, long ldb, double *dC, long ldc);

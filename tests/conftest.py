@@ -31,4 +31,9 @@ def gpu_lib(lib):
         cudart_ok = False
     if not cudart_ok:
         pytest.fail("GPU test selected but no CUDA device is visible: the product has no CPU path")
+    # The GPU suite's small shapes are there to exercise the tensor-core kernels and the host
+    # pipeline on ragged edges; by default the host-pointer call would route them to the one-kernel
+    # latency path (csrc/dgemm_small.cu).  That path has its own file, tests/test_gpu_dgemm_small.py,
+    # which switches it on and back off; smoke() and bench.py run the default configuration.
+    lib.mb200_set_dgemm_small_limit(0.0)
     return lib
