@@ -156,3 +156,28 @@ def test_small_path_nonfinite_b_propagates(gpu_lib):
         assert relerr(got[:, 2:3], want) <= 1e-13
     finally:
         api.free_compressed(h)
+
+
+@pytest.mark.parametrize("b_pinned,c_pinned", [(True, True), (True, False), (False, True)])
+def test_small_path_page_locked_panels(gpu_lib, b_pinned, c_pinned):
+    """Page-locked caller panels are copied directly, pageable ones through the pinned ring, in any
+    combination."""
+    import torch
+    from miraculix_b200 import api
+    snps, indiv, n = 4100, 300, 3
+    plink, Z, f = simulate.simulate(snps, indiv, seed=21, missing=0.01)
+    h = api.init_compressed(plink, snps, indiv, f, n)
+    try:
+        for tr, k, m in (("N", snps, indiv), ("T", indiv, snps)):
+            tb = torch.randn(n, k, dtype=torch.float64)         # row-major (n, k) == column-major k x n
+            tc = torch.full((n, m), 9.0, dtype=torch.float64)
+            if b_pinned:
+                tb = tb.pin_memory()
+            if c_pinned:
+                tc = tc.pin_memory()
+            gpu_lib.dgemm_compressed(tr.encode(), h, n, tb.data_ptr(), k, tc.data_ptr(), m)
+            assert gpu_lib.mb200_last_status() == 0 and used_small_path(gpu_lib, h)
+            want = cport.dgemm_compressed(tr, plink, snps, indiv, f, tb.numpy().T, True)
+            assert relerr(tc.numpy().T, want) <= 1e-13
+    finally:
+        api.free_compressed(h)
