@@ -94,7 +94,7 @@ struct DevCtx {
   double *P[2] = {nullptr, nullptr}, *PT[2] = {nullptr, nullptr};
   cudaEvent_t fin[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr}, up = nullptr;
   cudaEvent_t t0 = nullptr, t1 = nullptr;
-  Stager stager;
+  Stager *stager = nullptr;  // leased per call from the parked rings (stager.h)
   std::vector<BandPlan> plans;
   double ops = 0.0;
   void release() {
@@ -115,7 +115,8 @@ struct DevCtx {
     if (up) cudaEventDestroy(up);
     if (t0) cudaEventDestroy(t0);
     if (t1) cudaEventDestroy(t1);
-    stager.destroy();
+    stager_release(stager);
+    stager = nullptr;
     if (s_main) cudaStreamDestroy(s_main);
     if (s_copy) cudaStreamDestroy(s_copy);
   }
@@ -129,7 +130,7 @@ int upload_bytes(DevCtx &c, bool pinned, uint8_t *d, const uint8_t *h, size_t by
     return 0;
   }
   const size_t whole = bytes / 8;  // the ring moves doubles; the (< 8 byte) tail goes directly
-  if (whole) MB_CHECK(c.stager.upload(reinterpret_cast<double *>(d), (long)whole,
+  if (whole) MB_CHECK(c.stager->upload(reinterpret_cast<double *>(d), (long)whole,
                                       reinterpret_cast<const double *>(h), (long)whole, (long)whole, 1, c.s_main));
   if (bytes % 8) MB_CUDA(cudaMemcpyAsync(d + whole * 8, h + whole * 8, bytes % 8, cudaMemcpyHostToDevice, c.s_main));
   return 0;
@@ -241,7 +242,10 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
     MB_CUDA(cudaEventCreateWithFlags(&c.up, cudaEventDisableTiming));
     MB_CUDA(cudaEventCreate(&c.t0));
     MB_CUDA(cudaEventCreate(&c.t1));
-    if (!ans_pin || !x_pin) MB_CHECK(c.stager.init(4u << 20));
+    if (!ans_pin || !x_pin) {
+      c.stager = stager_acquire(c.device, 4u << 20);
+      if (!c.stager) return status().code ? status().code : fail(-1, __func__, __LINE__, "no pinned staging ring");
+    }
     // scratch from the library's pool (cached between calls: a GBLUP script calls this repeatedly)
     // the packed matrix is read by the peers (the library pool grants them access, abi.cu)
     MB_CUDA(pool_alloc(&c.d_x, (size_t)rows * nb, c.s_main));
@@ -297,16 +301,16 @@ int crossprod_host_tiled(const uint8_t *x, long k, long rows, double *ans, int i
         MB_CUDA(cudaEventRecord(c.fin[buf], c.s_main));
         MB_CUDA(cudaStreamWaitEvent(c.s_copy, c.fin[buf], 0));
         // rows of the panel = columns c0.. of ans, from row c0 down (contiguous runs of n - c0)
-        MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.P[buf], w, w, (int)crows, c.s_copy));
+        MB_CHECK(panel_d2h(c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.P[buf], w, w, (int)crows, c.s_copy));
         // transposed panel = rows c0.. of the columns from c0 on (runs of crows)
-        MB_CHECK(panel_d2h(&c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.PT[buf], crows, crows, (int)w, c.s_copy));
+        MB_CHECK(panel_d2h(c.stager, ans_pin, ans + c0 + c0 * rows, rows, c.PT[buf], crows, crows, (int)w, c.s_copy));
         MB_CUDA(cudaEventRecord(c.freed[buf], c.s_copy));
         used[buf] = true;
       }
     }
     MB_CUDA(cudaEventRecord(c.t1, c.s_main));
     if (g == 0) debug_info("  all work enqueued at %.2f ms", since());
-    if (!ans_pin) MB_CHECK(c.stager.drain());
+    if (!ans_pin) MB_CHECK(c.stager->drain());
     MB_CUDA(cudaStreamSynchronize(c.s_main));
     MB_CUDA(cudaStreamSynchronize(c.s_copy));
     if (g == 0) debug_info("  streams drained at %.2f ms", since());

@@ -2,6 +2,9 @@
 #include "stager.h"
 #include <stdlib.h>
 #include <string.h>
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
@@ -27,7 +30,45 @@ struct CopyJob {
   size_t pieces = 0, piece_bytes = 0;  // the flattened width*height bytes are cut into pieces
   std::atomic<size_t> next{0};
   int helpers_in = 0;                  // helpers working on this job (guarded by the pool mutex)
+  bool streaming = false;              // non-temporal stores (large copies)
 };
+
+// Large copies bypass the cache on the store side: a staged panel is written once and read next by
+// the DMA engine or, much later, by the caller, and a regular store first READS the destination line
+// (write-allocate) -- three DRAM transfers per byte instead of two, on copies that run at the host's
+// memory bandwidth (the pageable configs[4] GRM stages 105 GB).  SSE2 streaming stores are part of
+// x86-64; other hosts use memcpy.
+#if defined(__x86_64__)
+void stream_copy(uint8_t *d, const uint8_t *s, size_t n) {
+  if (n < 512) {
+    memcpy(d, s, n);
+    return;
+  }
+  const size_t head = (size_t)(-(intptr_t)d) & 63;  // up to the next 64-byte line of the destination
+  if (head) {
+    memcpy(d, s, head);
+    d += head;
+    s += head;
+    n -= head;
+  }
+  const size_t body = n & ~(size_t)63;
+  for (size_t i = 0; i < body; i += 64) {
+    const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i *>(s + i));
+    const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i *>(s + i + 16));
+    const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i *>(s + i + 32));
+    const __m128i e = _mm_loadu_si128(reinterpret_cast<const __m128i *>(s + i + 48));
+    _mm_stream_si128(reinterpret_cast<__m128i *>(d + i), a);
+    _mm_stream_si128(reinterpret_cast<__m128i *>(d + i + 16), b);
+    _mm_stream_si128(reinterpret_cast<__m128i *>(d + i + 32), c);
+    _mm_stream_si128(reinterpret_cast<__m128i *>(d + i + 48), e);
+  }
+  if (n > body) memcpy(d + body, s + body, n - body);
+}
+inline void stream_fence() { _mm_sfence(); }
+#else
+void stream_copy(uint8_t *d, const uint8_t *s, size_t n) { memcpy(d, s, n); }
+inline void stream_fence() {}
+#endif
 
 void copy_piece(const CopyJob &j, size_t piece) {
   size_t b0 = piece * j.piece_bytes;
@@ -36,9 +77,11 @@ void copy_piece(const CopyJob &j, size_t piece) {
   while (b0 < b1) {  // a piece may span several columns
     const size_t col = b0 / j.width, off = b0 % j.width;
     const size_t n = j.width - off < b1 - b0 ? j.width - off : b1 - b0;
-    memcpy(j.dst + col * j.dpitch + off, j.src + col * j.spitch + off, n);
+    if (j.streaming) stream_copy(j.dst + col * j.dpitch + off, j.src + col * j.spitch + off, n);
+    else memcpy(j.dst + col * j.dpitch + off, j.src + col * j.spitch + off, n);
     b0 += n;
   }
+  if (j.streaming) stream_fence();  // the piece is globally visible before it is reported done
 }
 
 class CopyPool {
@@ -142,6 +185,11 @@ void parallel_copy_2d(void *dst, size_t dpitch, const void *src, size_t spitch, 
   job.spitch = spitch;
   job.width = width;
   job.height = height;
+  static const size_t stream_min = [] {  // MB200_COPY_STREAM_MIN: bytes from which stores bypass the cache (0 = never)
+    const char *e = getenv("MB200_COPY_STREAM_MIN");
+    return e ? (size_t)atof(e) : (size_t)(1 << 20);
+  }();
+  job.streaming = stream_min > 0 && total >= stream_min;
   constexpr size_t kMinPiece = 256 << 10;  // below ~256 KB per thread the hand-off costs more
   CopyPool &pool = CopyPool::get();
   const size_t parts = (size_t)pool.helpers() + 1;
@@ -269,6 +317,53 @@ int Stager::download(double *h, long ld_h, const double *d, long ld_d, long rows
     }
   }
   return 0;
+}
+
+namespace {
+std::mutex g_park_mu;
+std::vector<Stager *> g_parked;  // idle rings, any device
+constexpr size_t kMaxParkedPerDevice = 2;
+}  // namespace
+
+Stager *stager_acquire(int device, size_t slot_bytes) {
+  {
+    std::lock_guard<std::mutex> lk(g_park_mu);
+    for (size_t i = 0; i < g_parked.size(); i++) {
+      Stager *s = g_parked[i];
+      if (s->device == device && s->slot_bytes == slot_bytes) {
+        g_parked[i] = g_parked.back();
+        g_parked.pop_back();
+        s->parked = false;
+        return s;
+      }
+    }
+  }
+  Stager *s = new Stager();
+  s->device = device;
+  if (s->init(slot_bytes) != 0) {
+    s->destroy();
+    delete s;
+    return nullptr;
+  }
+  return s;
+}
+
+void stager_release(Stager *s) {
+  if (!s) return;
+  s->drain();  // nothing of this call stays in flight
+  {
+    std::lock_guard<std::mutex> lk(g_park_mu);
+    size_t same = 0;
+    for (Stager *p : g_parked) same += p->device == s->device;
+    if (same < kMaxParkedPerDevice) {
+      s->parked = true;
+      s->next = 0;
+      g_parked.push_back(s);
+      return;
+    }
+  }
+  s->destroy();
+  delete s;
 }
 
 static cudaError_t copy2d_direct(void *dst, long dld, const void *src, long sld, long rows, int cols,

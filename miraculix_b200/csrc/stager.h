@@ -34,6 +34,8 @@ struct Stager {
     int cols = 0;
   } pend[kSlots];
   int next = 0;
+  int device = -1;   // set by stager_acquire
+  bool parked = false;
 
   int init(size_t slot_bytes_);
   void destroy();
@@ -46,6 +48,13 @@ struct Stager {
   int acquire(int *slot);
   int retire(int slot);
 };
+
+// Rings kept between calls: cudaHostAlloc + cudaFreeHost of a 24 MB ring cost 20-40 ms, more than a
+// whole configs[1] GRM.  stager_acquire hands out an initialised ring for `device` (which must be the
+// current device) -- a cached one when one is free, a new one otherwise -- and stager_release parks
+// it for the next call (at most a few per device stay cached; they are never freed before exit).
+Stager *stager_acquire(int device, size_t slot_bytes);
+void stager_release(Stager *s);
 
 // Copy a rows x cols column-major block between host and device, directly when the host side is
 // page-locked, through the stager otherwise.  Downloads through the stager complete at drain().
