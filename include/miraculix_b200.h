@@ -158,6 +158,9 @@ int mb200_set_dgemm_wide_cluster(int on);
  * 'T') with the kernels by cutting the SNP axis into `chunks` pieces (default 4, at most 16;
  * boundaries multiples of 512 SNPs), fewer when a chunk would hold less than min_bytes of that
  * panel (default 1e7: a 10 MB panel is not cut at all; 0 = always `chunks`; negative = keep).
+ * With page-locked panels the handle measures the rate of its own copies (events around the
+ * largest chunk of the previous call) and picks the count <= `chunks` that minimises exposed copy
+ * + 50 us per chunk: boxes whose GPUs share host links deliver a fraction of a link per device.
  * Results do not depend on the chunking beyond fp64 summation order. */
 int mb200_set_pipeline(int chunks, double min_bytes);
 /* Host-pointer dgemm_compressed on SMALL problems (snps * indiv * n <= products, panels below

@@ -172,3 +172,32 @@ def test_copy_pool_serves_concurrent_callers(lib):
     assert lib.mb200_debug_parallel_copy(out.ctypes.data, big.size, big.ctypes.data, big.size, big.size, 1) == 0
     assert np.array_equal(out, big)
     assert lib.mb200_debug_parallel_copy(None, 8, big.ctypes.data, 8, 8, 1) != 0
+
+
+def test_c_demo_compiles_as_c99_and_fails_loudly_without_a_gpu(lib):
+    """examples/c_abi_demo.c: the reference's call sequence in plain C.  The header must be valid
+    C99 (the bindings are C / Fortran / Julia), the program must link against the in-tree library,
+    and on a box without a GPU it must report the missing device instead of computing anything."""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no gcc")
+    out = os.path.join(root, "miraculix_b200", "build", "c_abi_demo")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    libdir = os.path.join(root, "miraculix_b200")
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-Werror", "-O2", "-I", os.path.join(root, "include"),
+                        os.path.join(root, "examples", "c_abi_demo.c"), "-o", out, "-L", libdir,
+                        "-lmiraculix_b200", f"-Wl,-rpath,{libdir}", "-lm"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    run = subprocess.run([out], capture_output=True, text=True, timeout=300)
+    if has_gpu:
+        assert run.returncode == 0 and "ok" in run.stdout, run.stdout + run.stderr
+    else:
+        assert run.returncode == 2 and "no handle" in run.stdout and "no CPU path" in run.stdout, run.stdout
