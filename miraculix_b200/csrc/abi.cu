@@ -215,6 +215,7 @@ void destroy_handle(Handle *h) {
   cudaFree(h->d_cg);
   if (h->h_cg) cudaFreeHost(h->h_cg);
   if (h->h_pipe) cudaFreeHost(h->h_pipe);
+  if (h->h_small) cudaFreeHost(h->h_small);
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int i = 0; i < Handle::kPipeMax; i++)
     if (h->ev_pipe[i]) cudaEventDestroy(h->ev_pipe[i]);

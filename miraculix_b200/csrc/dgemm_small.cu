@@ -162,8 +162,7 @@ int dgemm_small_device(Handle *h, int trans, int n, const double *dB, long ldb, 
 }
 
 // Does the host-pointer call take this path?  Work limit in genotype x column products
-// (mb200_set_dgemm_small_limit / MB200_SMALL_LIMIT, 0 = never); each panel fits one slot of the
-// handle's pinned ring.
+// (mb200_set_dgemm_small_limit / MB200_SMALL_LIMIT, 0 = never); panels of at most 4 MB each.
 bool dgemm_small_applies(const Handle *h, int n) {
   const Options &o = options();
   if (o.small_limit <= 0 || o.dgemm_mode != 1 || o.dgemm_slices != 0) return false;
@@ -173,31 +172,37 @@ bool dgemm_small_applies(const Handle *h, int n) {
 }
 
 // Host panels: upload, one launch per column group, download, ONE synchronisation.  Pageable
-// panels (what the bindings pass) are copied by the host into / out of two slots of the handle's
-// pinned ring: cudaMemcpyAsync on pageable memory synchronises inside the driver, twice per call.
+// panels (what the bindings pass) are copied by the host into / out of a small pinned buffer of the
+// handle: cudaMemcpyAsync on pageable memory synchronises inside the driver, twice per call.
 int dgemm_small_host(Handle *h, int trans, int n, const double *B, long ldb, double *C, long ldc) {
   const long m = trans ? h->snps : h->indiv, k = trans ? h->indiv : h->snps;
   const bool b_pin = host_is_pinned(B), c_pin = host_is_pinned(C);
-  Stager *sg = &h->stager;
   const double *srcB = B;
   long ld_src = ldb;
   double *dstC = C;
   long ld_dst = ldc;
   if (!b_pin || !c_pin) {
-    MB_CHECK(sg->init(4u << 20));
-    MB_CHECK(sg->drain());  // no staged copy of an earlier call is in flight: the slots are free
+    const size_t b_bytes = b_pin ? 0 : round_up((long)sizeof(double) * k * n, 256);
+    const size_t c_bytes = c_pin ? 0 : sizeof(double) * m * n;
+    if (b_bytes + c_bytes > h->h_small_bytes) {
+      if (h->h_small) MB_CUDA(cudaFreeHost(h->h_small));
+      h->h_small = nullptr;
+      h->h_small_bytes = 0;
+      const size_t want = (size_t)round_up((long)(b_bytes + c_bytes), 65536);
+      MB_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&h->h_small), want, cudaHostAllocPortable));
+      h->h_small_bytes = want;
+    }
     if (!b_pin) {
-      double *slot = reinterpret_cast<double *>(sg->ring);
+      double *slot = reinterpret_cast<double *>(h->h_small);
       parallel_copy_2d(slot, sizeof(double) * k, B, sizeof(double) * ldb, sizeof(double) * k, (size_t)n);
       srcB = slot;
       ld_src = k;
     }
     if (!c_pin) {
-      dstC = reinterpret_cast<double *>(sg->ring + sg->slot_bytes);
+      dstC = reinterpret_cast<double *>(h->h_small + b_bytes);
       ld_dst = m;
     }
   }
-
   if (ld_src == k)
     MB_CUDA(cudaMemcpyAsync(h->d_B, srcB, sizeof(double) * k * n, cudaMemcpyHostToDevice, h->stream));
   else

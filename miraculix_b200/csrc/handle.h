@@ -65,6 +65,10 @@ struct Handle {
   static constexpr int kPipeMax = 16;
   cudaEvent_t ev_pipe[kPipeMax] = {nullptr};
   void *h_pipe = nullptr;  // pinned word: the precision flag travels back with the result
+  // pinned staging of the latency path (dgemm_small.cu): just the two small panels, grown on demand --
+  // a first call must not pay for the 24 MB ring (20-40 ms of page pinning)
+  uint8_t *h_small = nullptr;
+  size_t h_small_bytes = 0;
   // measured rate of this handle's pinned host copies (GB/s; [0] H2D of 'N', [1] D2H of 'T'): events
   // around the largest chunk of the last call; the chunk count of the next call follows from it
   // (boxes whose GPUs share host links deliver a fraction of a link per device)
