@@ -145,3 +145,28 @@ def test_oracle_cg_restatement_solves_the_dense_system():
     assert np.abs(x - np.linalg.solve(G, b)).max() <= 1e-9 * np.abs(x).max()
     v = rng.standard_normal(indiv)
     assert np.abs(ocg.grm_vec(plink, snps, indiv, f, v) - Zc @ (Zc.T @ v)).max() <= 1e-9 * snps
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref/ref_miraculix.so not built")
+@pytest.mark.parametrize("seed", range(8))
+def test_oracle_matches_live_reference_on_random_shapes(seed):
+    """Seeded random ragged shapes, missing codes, centred or not, an EXTERNAL f that is not the
+    data's allele frequency (the GPU mode of the reference requires caller-supplied f,
+    5codesChar.cc:192-193), 1..17 columns: the restatement against the reference CPU library."""
+    rng = np.random.default_rng(1000 + seed)
+    snps, indiv = int(rng.integers(1, 3000)), int(rng.integers(1, 1200))
+    ncol = int(rng.integers(1, 18))
+    centered = bool(seed % 2 == 0)
+    plink, Z, f = simulate.simulate(snps, indiv, seed=seed, missing=float(rng.choice([0.0, 0.01, 0.2])))
+    if seed % 3 == 0:
+        f = rng.uniform(0.0, 1.0, snps)
+    ref.set_options(cores=2, centered=centered)
+    h = ref.RefCompressed(plink, snps, indiv, f, ncol)
+    try:
+        for tr, k in (("N", snps), ("T", indiv)):
+            B = np.asfortranarray(rng.standard_normal((k, ncol)) * 10.0 ** float(rng.integers(-3, 4)))
+            got = cport.dgemm_compressed(tr, plink, snps, indiv, f, B, centered)
+            assert relerr(got, h.dgemm(tr, B)) <= TOL, (snps, indiv, ncol, tr, centered)
+    finally:
+        h.free()
+        ref.set_options(cores=4, centered=True)
